@@ -1,0 +1,911 @@
+// kvx.cu — host side of libkvx.so: the C ABI declared in include/kvx.h over the sm_100a kernels in
+// kvx_kernels.cuh.  No torch types, no CPU fallback: every compute entry needs a CUDA device.
+#include "kvx.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kvx_kernels.cuh"
+
+using kvx::XferParams;
+using kvx::XferSide;
+
+namespace {
+
+constexpr uint32_t kNumFlags = 4096;     // completion flags per context (uint64 each)
+constexpr uint32_t kNumCounters = 1024;  // done-counter ring (one per launch that carries a flag)
+constexpr uint32_t kTableRing = 1u << 22;  // int32 entries of device scratch for host block tables
+constexpr uint32_t kMemMagic = 0x4d58564bu;   // "KVXM"
+constexpr uint32_t kPoolMagic = 0x5058564bu;  // "KVXP"
+
+struct MemRecord {  // wire format of one exported device buffer
+  uint32_t magic;
+  int32_t device;
+  int64_t pid;
+  uint64_t raw_ptr;
+  uint64_t offset;  // raw_ptr - allocation base
+  uint64_t bytes;
+  cudaIpcMemHandle_t handle;
+};
+
+struct PoolRecordHeader {  // wire format of an exported pool: header + regions x MemRecord
+  uint32_t magic;
+  uint32_t regions;
+  uint32_t block_tokens, heads, head_dim, elem_bytes, layout, tp_rank, tp_size, reserved;
+  uint64_t num_blocks, block_stride;
+};
+
+// Peer allocations opened in this process, by handle bytes: a handle may be opened once.
+struct IpcMapping {
+  void* base;
+  int refs;
+};
+std::mutex g_ipc_mu;
+std::map<std::string, IpcMapping> g_ipc_open;
+
+}  // namespace
+
+struct kvx_ctx {
+  int device = 0;
+  int sms = 0;
+  int64_t opt[KVX_OPT__COUNT] = {0};
+  uint64_t launches = 0;
+  uint64_t* d_flags = nullptr;
+  unsigned* d_counters = nullptr;
+  unsigned* d_status = nullptr;
+  int* d_table_ring = nullptr;
+  uint32_t counter_cursor = 0;
+  uint32_t table_cursor = 0;
+  cudaStream_t aux = nullptr;
+  std::string last_error;
+  std::map<void*, std::string> imported;  // imported pointer → handle key ("" = same process)
+};
+
+struct kvx_pool {
+  kvx_ctx* ctx = nullptr;
+  kvx_pool_desc desc{};
+  std::vector<void*> base;
+  std::vector<void*> imported_ptrs;  // to unmap on release
+  unsigned long long* d_bases = nullptr;
+  uint64_t chunk_bytes = 0;
+};
+
+namespace {
+
+int32_t cuda_fail(kvx_ctx* ctx, cudaError_t e, const char* what) {
+  if (ctx) {
+    ctx->last_error = std::string(what) + ": " + cudaGetErrorName(e) + " (" + cudaGetErrorString(e) + ")";
+  }
+  (void)cudaGetLastError();
+  return KVX_ECUDA;
+}
+#define KVX_CUDA(ctx, call)                                    \
+  do {                                                         \
+    cudaError_t e__ = (call);                                  \
+    if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess) ok = true;
+  }
+  ~DeviceGuard() {
+    if (ok && prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int64_t env_or(const char* name, int64_t dflt) {
+  const char* v = getenv(name);
+  if (!v || !*v) return dflt;
+  return strtoll(v, nullptr, 0);
+}
+
+// ---- geometry ---------------------------------------------------------------------------------
+struct ChunkGeom {  // one side's chunk: H heads in `layout`, slice starts at head `off`
+  uint32_t layout, heads, off;
+};
+
+struct Plan {
+  uint32_t ppc, piece_bytes;
+  uint32_t s_runs, s_run_bytes, s_stride, s_slice_off, s_piece_stride;
+  uint32_t d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b, d_slice_off, d_piece_stride;
+};
+
+// Split a slice of Hc heads x N tokens x R bytes into pieces of at most `cap` bytes and describe
+// each piece as source runs / destination runs (see XferParams).  Pieces split along the source's
+// major dimension (tokens for NHD, heads for HND) so that both sides stay a 2-level run pattern.
+int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d, uint32_t cap, Plan* out) {
+  if (Hc == 0 || N == 0 || R == 0 || (R % 16u) != 0) return KVX_EUNSUPPORTED;
+  if (s.off + Hc > s.heads || d.off + Hc > d.heads) return KVX_EINVAL;
+  const bool src_hnd = s.layout == KVX_LAYOUT_HND;
+  const bool dst_hnd = d.layout == KVX_LAYOUT_HND;
+  const uint32_t major = src_hnd ? Hc : N;
+  const uint32_t unit_bytes = src_hnd ? N * R : Hc * R;
+  if (unit_bytes > cap) return KVX_EUNSUPPORTED;
+  uint32_t g = 1;
+  for (uint32_t c = major; c >= 1; --c) {
+    if (major % c == 0 && static_cast<uint64_t>(c) * unit_bytes <= cap) {
+      g = c;
+      break;
+    }
+  }
+  Plan p{};
+  p.ppc = major / g;
+  p.piece_bytes = g * unit_bytes;
+  if (src_hnd) {
+    // source slice [off, off+Hc) heads is contiguous: Hc * N * R bytes
+    p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0;
+    p.s_slice_off = s.off * N * R; p.s_piece_stride = g * N * R;
+    if (dst_hnd) {
+      p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; p.d_stride_b = 0;
+      p.d_slice_off = d.off * N * R; p.d_piece_stride = g * N * R;
+    } else {
+      // image order (h, t) → NHD row (t, off+h): run x = h*N + t
+      p.d_runs = g * N; p.d_run_bytes = R; p.d_n1 = N; p.d_stride_a = R; p.d_stride_b = d.heads * R;
+      p.d_slice_off = d.off * R; p.d_piece_stride = g * R;
+    }
+  } else {
+    if (Hc == s.heads) {
+      p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; p.s_slice_off = 0;
+    } else {
+      p.s_runs = g; p.s_run_bytes = Hc * R; p.s_stride = s.heads * R; p.s_slice_off = s.off * R;
+    }
+    p.s_piece_stride = g * s.heads * R;
+    if (!dst_hnd) {
+      if (Hc == d.heads) {
+        p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; p.d_stride_b = 0;
+        p.d_slice_off = 0;
+      } else {
+        p.d_runs = g; p.d_run_bytes = Hc * R; p.d_n1 = 1; p.d_stride_a = d.heads * R; p.d_stride_b = 0;
+        p.d_slice_off = d.off * R;
+      }
+      p.d_piece_stride = g * d.heads * R;
+    } else {
+      // image order (t, h) → HND row (off+h, t): run x = t*Hc + h
+      p.d_runs = g * Hc; p.d_run_bytes = R; p.d_n1 = Hc; p.d_stride_a = R; p.d_stride_b = N * R;
+      p.d_slice_off = d.off * N * R; p.d_piece_stride = g * R;
+    }
+  }
+  *out = p;
+  return KVX_OK;
+}
+
+enum Engine { kEngineAuto = 0, kEngineLdg = 1, kEngineTma = 2 };
+
+struct LaunchSpec {  // what a transfer needs besides geometry
+  XferSide src{}, dst{};
+  uint32_t n = 0, regions = 0;
+  uint32_t N = 0, R = 0, Hc = 0;
+  ChunkGeom sg{}, dg{};
+  uint64_t* flag = nullptr;
+  uint64_t flag_val = 0;
+  bool copy_mode = false;  // contiguous→contiguous bytes (kvx_copy)
+  uint64_t copy_bytes = 0;
+};
+
+bool all_aligned(uint64_t a, const Plan& pl, const XferSide& s, const XferSide& d) {
+  auto m = [a](uint64_t v) { return (v % a) == 0; };
+  return m(pl.s_run_bytes) && m(pl.d_run_bytes) && m(pl.s_stride) && m(pl.d_stride_a) && m(pl.d_stride_b) &&
+         m(pl.s_slice_off) && m(pl.d_slice_off) && m(pl.s_piece_stride) && m(pl.d_piece_stride) &&
+         m(s.block_stride) && m(d.block_stride) && m(s.base0) && m(d.base0);
+}
+
+template <typename K>
+int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
+  KVX_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+  return KVX_OK;
+}
+
+int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>* src_bases,
+                    const std::vector<void*>* dst_bases, cudaStream_t stream) {
+  DeviceGuard guard(ctx->device);
+  if (!guard.ok) return cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice");
+
+  int engine = static_cast<int>(ctx->opt[KVX_OPT_ENGINE]);
+  const uint32_t stages = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGES]);
+  const uint32_t stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
+  uint32_t cons_warps = static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]);
+  const uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
+  const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
+  int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);
+  if (engine == kEngineAuto) engine = kEngineTma;
+
+  constexpr uint32_t kLdgThreads = 256;
+  // KMAX by vector width: 8 units of 16 B or 4 units of 32 B per thread.
+  const uint32_t ldg_cap16 = kLdgThreads * 8u * 16u, ldg_cap32 = kLdgThreads * 4u * 32u;
+
+  XferParams p{};
+  p.src = ls.src;
+  p.dst = ls.dst;
+  p.n = ls.n;
+  p.regions = ls.regions;
+  Plan pl{};
+  if (ls.copy_mode) {
+    uint32_t piece = engine == kEngineTma ? stage_bytes : ldg_cap16;
+    if (engine == kEngineTma && store_mode == 1) piece = std::min<uint32_t>(piece, cons_warps * 32u * 8u * 16u);
+    const uint64_t items = (ls.copy_bytes + piece - 1) / piece;
+    if (items == 0) return KVX_OK;
+    if (items >= (1ull << 31)) return KVX_EUNSUPPORTED;
+    pl.ppc = 1; pl.piece_bytes = piece;
+    pl.s_runs = 1; pl.s_run_bytes = piece; pl.d_runs = 1; pl.d_run_bytes = piece; pl.d_n1 = 1;
+    p.n = static_cast<uint32_t>(items);
+    p.regions = 1;
+    p.src.block_stride = piece;
+    p.dst.block_stride = piece;
+    const uint64_t tail = ls.copy_bytes - (items - 1) * piece;
+    p.tail_bytes = tail == piece ? 0u : static_cast<uint32_t>(tail);
+  } else {
+    uint32_t cap;
+    if (engine == kEngineTma) {
+      cap = stage_bytes;
+    } else {
+      cap = ldg_cap16;
+    }
+    int32_t rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, cap, &pl);
+    if (rc == KVX_EUNSUPPORTED && engine == kEngineTma) {  // unit larger than a stage: register path
+      engine = kEngineLdg;
+      rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, ldg_cap16, &pl);
+    }
+    if (rc != KVX_OK) return rc;
+    p.src.slice_off = pl.s_slice_off; p.src.piece_stride = pl.s_piece_stride;
+    p.dst.slice_off = pl.d_slice_off; p.dst.piece_stride = pl.d_piece_stride;
+  }
+  const uint64_t total = static_cast<uint64_t>(p.n) * p.regions * pl.ppc;
+  if (total == 0) {
+    if (ls.flag) {  // empty request (full prefix hit): notify only
+      KVX_CUDA(ctx, cudaMemcpyAsync(ls.flag, &ls.flag_val, sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
+    }
+    return KVX_OK;
+  }
+  if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;
+  p.total_items = static_cast<uint32_t>(total);
+  p.ppc = pl.ppc; p.piece_bytes = pl.piece_bytes;
+  p.s_runs = pl.s_runs; p.s_run_bytes = pl.s_run_bytes; p.s_stride = pl.s_stride;
+  p.d_runs = pl.d_runs; p.d_run_bytes = pl.d_run_bytes; p.d_n1 = pl.d_n1;
+  p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
+  p.stages = stages; p.stage_bytes = stage_bytes;
+  p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
+  p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
+  p.flag_val = ls.flag_val;
+  p.status = ctx->d_status;
+  p.done_counter = ctx->d_counters + (ctx->counter_cursor++ % kNumCounters);
+
+  // 32-byte accesses need every address component 32-byte aligned (region bases included).
+  bool ok32 = all_aligned(32, pl, p.src, p.dst);
+  if (ok32 && src_bases) for (void* b : *src_bases) ok32 = ok32 && (reinterpret_cast<uintptr_t>(b) % 32 == 0);
+  if (ok32 && dst_bases) for (void* b : *dst_bases) ok32 = ok32 && (reinterpret_cast<uintptr_t>(b) % 32 == 0);
+  if (p.tail_bytes % 32 != 0) ok32 = false;
+  if (vec_opt == 0) vec_opt = ok32 ? 32 : 16;
+  if (vec_opt == 32 && !ok32) vec_opt = 16;
+
+  const uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
+  const uint32_t grid = std::min<uint32_t>(max_ctas, p.total_items);
+
+  if (engine == kEngineTma) {
+    const bool dst_single_run = pl.d_runs == 1;
+    int mode = store_mode;  // 1 thread stores, 2 bulk stores
+    if (mode == 0) mode = dst_single_run ? 2 : 1;
+    const size_t smem = static_cast<size_t>(stages) * stage_bytes;
+    if (mode == 2) {
+      if (stages < 2) return KVX_EINVAL;
+      auto k = kvx::kvx_xfer_tma_kernel<0, 1>;
+      int32_t rc = set_smem(ctx, k, smem);
+      if (rc) return rc;
+      k<<<grid, 32u * (1u + cons_warps), smem, stream>>>(p);
+    } else {
+      const uint32_t T = cons_warps * 32u;
+      if (vec_opt == 32 && static_cast<uint64_t>(T) * 4u * 32u >= pl.piece_bytes) {
+        auto k = kvx::kvx_xfer_tma_kernel<32, 4>;
+        int32_t rc = set_smem(ctx, k, smem);
+        if (rc) return rc;
+        k<<<grid, 32u + T, smem, stream>>>(p);
+      } else if (static_cast<uint64_t>(T) * 8u * 16u >= pl.piece_bytes) {
+        auto k = kvx::kvx_xfer_tma_kernel<16, 8>;
+        int32_t rc = set_smem(ctx, k, smem);
+        if (rc) return rc;
+        k<<<grid, 32u + T, smem, stream>>>(p);
+      } else {
+        return KVX_EINVAL;  // stage larger than the consumer threads can drain: raise CONSUMER_WARPS
+      }
+    }
+  } else {
+    if (vec_opt == 32 && pl.piece_bytes <= ldg_cap32) {
+      kvx::kvx_xfer_ldg_kernel<32, 4><<<grid, kLdgThreads, 0, stream>>>(p);
+    } else {
+      kvx::kvx_xfer_ldg_kernel<16, 8><<<grid, kLdgThreads, 0, stream>>>(p);
+    }
+  }
+  KVX_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return KVX_OK;
+}
+
+int32_t resolve_xform(const kvx_pool_desc* src, const kvx_pool_desc* dst, const kvx_xform* xf, uint32_t* s_off,
+                      uint32_t* d_off, uint32_t* heads, uint32_t* stage_layout, uint32_t dflt_layout) {
+  uint32_t so = 0, dof = 0, hc = 0, sl = dflt_layout;
+  if (xf) {
+    so = xf->src_head_off; dof = xf->dst_head_off; hc = xf->heads; sl = xf->stage_layout;
+  }
+  if (sl != KVX_LAYOUT_NHD && sl != KVX_LAYOUT_HND) return KVX_EINVAL;
+  if (hc == 0) {
+    uint32_t a = src ? src->heads - std::min(so, src->heads) : UINT32_MAX;
+    uint32_t b = dst ? dst->heads - std::min(dof, dst->heads) : UINT32_MAX;
+    hc = std::min(a, b);
+  }
+  if (hc == 0) return KVX_EINVAL;
+  if (src && so + hc > src->heads) return KVX_EINVAL;
+  if (dst && dof + hc > dst->heads) return KVX_EINVAL;
+  *s_off = so; *d_off = dof; *heads = hc; *stage_layout = sl;
+  return KVX_OK;
+}
+
+XferSide paged_side(const kvx_pool* pool, const int32_t* table) {
+  XferSide s{};
+  s.bases = pool->d_bases;
+  s.table = table;
+  s.block_stride = pool->desc.block_stride;
+  s.num_blocks = pool->desc.num_blocks;
+  return s;
+}
+
+XferSide contiguous_side(const void* base, uint64_t chunk_bytes) {
+  XferSide s{};
+  s.bases = nullptr;
+  s.base0 = reinterpret_cast<uint64_t>(base);
+  s.block_stride = chunk_bytes;
+  return s;
+}
+
+bool same_shape(const kvx_pool_desc& a, const kvx_pool_desc& b) {
+  return a.regions == b.regions && a.block_tokens == b.block_tokens && a.head_dim == b.head_dim &&
+         a.elem_bytes == b.elem_bytes;
+}
+
+typedef CUresult (*PFN_cuMemGetAddressRange)(CUdeviceptr*, size_t*, CUdeviceptr);
+
+int32_t alloc_base_of(kvx_ctx* ctx, const void* ptr, uint64_t* base, uint64_t* size) {
+  static PFN_cuMemGetAddressRange fn = nullptr;
+  if (!fn) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    KVX_CUDA(ctx, cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &q));
+    if (!f || q != cudaDriverEntryPointSuccess) return KVX_EIPC;
+    fn = reinterpret_cast<PFN_cuMemGetAddressRange>(f);
+  }
+  CUdeviceptr b = 0;
+  size_t sz = 0;
+  if (fn(&b, &sz, reinterpret_cast<CUdeviceptr>(ptr)) != CUDA_SUCCESS) return KVX_EIPC;
+  *base = static_cast<uint64_t>(b);
+  *size = sz;
+  return KVX_OK;
+}
+
+int32_t export_record(kvx_ctx* ctx, const void* ptr, uint64_t bytes, MemRecord* rec) {
+  DeviceGuard guard(ctx->device);
+  memset(rec, 0, sizeof(*rec));
+  rec->magic = kMemMagic;
+  rec->device = ctx->device;
+  rec->pid = static_cast<int64_t>(getpid());
+  rec->raw_ptr = reinterpret_cast<uint64_t>(ptr);
+  rec->bytes = bytes;
+  uint64_t base = 0, size = 0;
+  int32_t rc = alloc_base_of(ctx, ptr, &base, &size);
+  if (rc) return rc;
+  rec->offset = rec->raw_ptr - base;
+  if (rec->offset + bytes > size) return KVX_EINVAL;
+  cudaError_t e = cudaIpcGetMemHandle(&rec->handle, reinterpret_cast<void*>(base));
+  if (e != cudaSuccess) {
+    // Not exportable (e.g. not a cudaMalloc allocation): still usable inside this process.
+    (void)cudaGetLastError();
+    memset(&rec->handle, 0, sizeof(rec->handle));
+  }
+  return KVX_OK;
+}
+
+int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out) {
+  if (rec->magic != kMemMagic) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  if (rec->pid == static_cast<int64_t>(getpid())) {
+    if (rec->device != ctx->device) {
+      int can = 0;
+      KVX_CUDA(ctx, cudaDeviceCanAccessPeer(&can, ctx->device, rec->device));
+      if (!can) return KVX_EIPC;
+      cudaError_t e = cudaDeviceEnablePeerAccess(rec->device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(ctx, e, "cudaDeviceEnablePeerAccess");
+      (void)cudaGetLastError();
+    }
+    *out = reinterpret_cast<void*>(rec->raw_ptr);
+    ctx->imported[*out] = std::string();
+    return KVX_OK;
+  }
+  const std::string key(reinterpret_cast<const char*>(&rec->handle), sizeof(rec->handle));
+  std::lock_guard<std::mutex> lk(g_ipc_mu);
+  auto it = g_ipc_open.find(key);
+  void* base = nullptr;
+  if (it != g_ipc_open.end()) {
+    base = it->second.base;
+    it->second.refs++;
+  } else {
+    cudaError_t e = cudaIpcOpenMemHandle(&base, rec->handle, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      cuda_fail(ctx, e, "cudaIpcOpenMemHandle");
+      return KVX_EIPC;
+    }
+    g_ipc_open[key] = IpcMapping{base, 1};
+  }
+  *out = static_cast<char*>(base) + rec->offset;
+  ctx->imported[*out] = key;
+  return KVX_OK;
+}
+
+int32_t unmap_ptr(kvx_ctx* ctx, void* ptr) {
+  auto it = ctx->imported.find(ptr);
+  if (it == ctx->imported.end()) return KVX_EINVAL;
+  const std::string key = it->second;
+  ctx->imported.erase(it);
+  if (key.empty()) return KVX_OK;
+  std::lock_guard<std::mutex> lk(g_ipc_mu);
+  auto m = g_ipc_open.find(key);
+  if (m != g_ipc_open.end() && --m->second.refs == 0) {
+    DeviceGuard guard(ctx->device);
+    cudaIpcCloseMemHandle(m->second.base);
+    g_ipc_open.erase(m);
+  }
+  return KVX_OK;
+}
+
+}  // namespace
+
+// =================================================================================================
+// C ABI
+// =================================================================================================
+extern "C" {
+
+uint32_t kvx_version(void) { return KVX_ABI_VERSION; }
+
+const char* kvx_strerror(int32_t code) {
+  switch (code) {
+    case KVX_OK: return "ok";
+    case KVX_EINVAL: return "invalid argument";
+    case KVX_ECUDA: return "CUDA error (see kvx_last_error)";
+    case KVX_ENOMEM: return "out of memory";
+    case KVX_EUNSUPPORTED: return "unsupported geometry";
+    case KVX_ETIMEOUT: return "timed out waiting for a completion flag";
+    case KVX_ERANGE: return "size out of range";
+    case KVX_EIPC: return "peer memory mapping failed";
+    case KVX_ENOTREADY: return "not ready";
+    default: return "unknown kvx error";
+  }
+}
+
+const char* kvx_last_error(const kvx_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
+
+int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
+  if (!out) return KVX_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) {
+    (void)cudaGetLastError();
+    return KVX_ECUDA;  // no CPU fallback
+  }
+  kvx_ctx* ctx = new (std::nothrow) kvx_ctx();
+  if (!ctx) return KVX_ENOMEM;
+  ctx->device = device;
+  DeviceGuard guard(device);
+  auto fail = [&](int32_t rc) {
+    kvx_ctx_destroy(ctx);
+    return rc;
+  };
+  if (!guard.ok) return fail(KVX_ECUDA);
+  if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return fail(KVX_ECUDA);
+  if (cudaMalloc(&ctx->d_flags, kNumFlags * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ENOMEM);
+  if (cudaMalloc(&ctx->d_counters, (kNumCounters + 1) * sizeof(unsigned)) != cudaSuccess) return fail(KVX_ENOMEM);
+  if (cudaMalloc(&ctx->d_table_ring, static_cast<size_t>(kTableRing) * sizeof(int)) != cudaSuccess) return fail(KVX_ENOMEM);
+  if (cudaMemset(ctx->d_flags, 0, kNumFlags * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ECUDA);
+  if (cudaMemset(ctx->d_counters, 0, (kNumCounters + 1) * sizeof(unsigned)) != cudaSuccess) return fail(KVX_ECUDA);
+  ctx->d_status = ctx->d_counters + kNumCounters;
+  if (cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking) != cudaSuccess) return fail(KVX_ECUDA);
+  ctx->opt[KVX_OPT_ENGINE] = env_or("KVX_ENGINE", 0);
+  ctx->opt[KVX_OPT_STAGES] = env_or("KVX_STAGES", 4);
+  ctx->opt[KVX_OPT_STAGE_BYTES] = env_or("KVX_STAGE_BYTES", 32768);
+  ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 1);
+  ctx->opt[KVX_OPT_STORE_MODE] = env_or("KVX_STORE_MODE", 0);
+  ctx->opt[KVX_OPT_VEC_BYTES] = env_or("KVX_VEC_BYTES", 0);
+  ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 8);
+  ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
+  *out = ctx;
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_destroy(kvx_ctx* ctx) {
+  if (!ctx) return KVX_EINVAL;
+  {
+    DeviceGuard guard(ctx->device);
+    if (guard.ok) {
+      cudaDeviceSynchronize();
+      while (!ctx->imported.empty()) unmap_ptr(ctx, ctx->imported.begin()->first);
+      if (ctx->aux) cudaStreamDestroy(ctx->aux);
+      cudaFree(ctx->d_flags);
+      cudaFree(ctx->d_counters);
+      cudaFree(ctx->d_table_ring);
+      (void)cudaGetLastError();
+    }
+  }
+  delete ctx;
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
+  if (!ctx || option < 0 || option >= KVX_OPT__COUNT) return KVX_EINVAL;
+  switch (option) {
+    case KVX_OPT_ENGINE: if (value < 0 || value > 2) return KVX_EINVAL; break;
+    case KVX_OPT_STAGES: if (value < 1 || value > kvx::kMaxStages) return KVX_EINVAL; break;
+    case KVX_OPT_STAGE_BYTES: if (value < 1024 || value > 200 * 1024 || value % 1024) return KVX_EINVAL; break;
+    case KVX_OPT_CTAS_PER_SM: if (value < 1 || value > 32) return KVX_EINVAL; break;
+    case KVX_OPT_STORE_MODE: if (value < 0 || value > 2) return KVX_EINVAL; break;
+    case KVX_OPT_VEC_BYTES: if (value != 0 && value != 16 && value != 32) return KVX_EINVAL; break;
+    case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
+    case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
+    default: break;
+  }
+  ctx->opt[option] = value;
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_get_option(const kvx_ctx* ctx, int32_t option, int64_t* value) {
+  if (!ctx || !value || option < 0 || option >= KVX_OPT__COUNT) return KVX_EINVAL;
+  *value = ctx->opt[option];
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_launch_count(const kvx_ctx* ctx, uint64_t* count) {
+  if (!ctx || !count) return KVX_EINVAL;
+  *count = ctx->launches;
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_sm_count(const kvx_ctx* ctx, int32_t* sms) {
+  if (!ctx || !sms) return KVX_EINVAL;
+  *sms = ctx->sms;
+  return KVX_OK;
+}
+
+int32_t kvx_mem_alloc(kvx_ctx* ctx, uint64_t bytes, void** out) {
+  if (!ctx || !out || bytes == 0) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  cudaError_t e = cudaMalloc(out, bytes);
+  if (e == cudaErrorMemoryAllocation) {
+    (void)cudaGetLastError();
+    return KVX_ENOMEM;
+  }
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaMalloc");
+  return KVX_OK;
+}
+
+int32_t kvx_mem_free(kvx_ctx* ctx, void* ptr) {
+  if (!ctx) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  KVX_CUDA(ctx, cudaFree(ptr));
+  return KVX_OK;
+}
+
+int32_t kvx_mem_export(kvx_ctx* ctx, const void* ptr, uint64_t bytes, void* buf, size_t* len) {
+  if (!ctx || !ptr || !len) return KVX_EINVAL;
+  if (!buf || *len < sizeof(MemRecord)) {
+    *len = sizeof(MemRecord);
+    return KVX_ERANGE;
+  }
+  MemRecord rec;
+  int32_t rc = export_record(ctx, ptr, bytes, &rec);
+  if (rc) return rc;
+  memcpy(buf, &rec, sizeof(rec));
+  *len = sizeof(rec);
+  return KVX_OK;
+}
+
+int32_t kvx_mem_import(kvx_ctx* ctx, const void* buf, size_t len, void** out) {
+  if (!ctx || !buf || !out || len < sizeof(MemRecord)) return KVX_EINVAL;
+  MemRecord rec;
+  memcpy(&rec, buf, sizeof(rec));
+  return import_record(ctx, &rec, out);
+}
+
+int32_t kvx_mem_unmap(kvx_ctx* ctx, void* imported) {
+  if (!ctx || !imported) return KVX_EINVAL;
+  return unmap_ptr(ctx, imported);
+}
+
+int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** out) {
+  if (!ctx || !desc || !out || !desc->base) return KVX_EINVAL;
+  if (desc->struct_size != sizeof(kvx_pool_desc)) return KVX_EINVAL;
+  if (desc->regions == 0 || desc->block_tokens == 0 || desc->heads == 0 || desc->head_dim == 0 ||
+      desc->elem_bytes == 0 || desc->num_blocks == 0)
+    return KVX_EINVAL;
+  if (desc->layout != KVX_LAYOUT_NHD && desc->layout != KVX_LAYOUT_HND) return KVX_EINVAL;
+  const uint64_t row = static_cast<uint64_t>(desc->head_dim) * desc->elem_bytes;
+  if (row % 16 != 0) return KVX_EUNSUPPORTED;  // 16-byte vector / bulk-copy granularity
+  const uint64_t chunk = row * desc->heads * desc->block_tokens;
+  if (chunk >= (1ull << 31)) return KVX_EUNSUPPORTED;
+  const uint64_t stride = desc->block_stride ? desc->block_stride : chunk;
+  if (stride < chunk || stride % 16 != 0) return KVX_EINVAL;
+  for (uint32_t r = 0; r < desc->regions; ++r) {
+    if (!desc->base[r] || reinterpret_cast<uintptr_t>(desc->base[r]) % 16 != 0) return KVX_EINVAL;
+  }
+  kvx_pool* pool = new (std::nothrow) kvx_pool();
+  if (!pool) return KVX_ENOMEM;
+  pool->ctx = ctx;
+  pool->desc = *desc;
+  pool->desc.block_stride = stride;
+  pool->base.assign(desc->base, desc->base + desc->regions);
+  pool->desc.base = pool->base.data();
+  pool->chunk_bytes = chunk;
+  DeviceGuard guard(ctx->device);
+  cudaError_t e = cudaMalloc(&pool->d_bases, desc->regions * sizeof(unsigned long long));
+  if (e == cudaSuccess)
+    e = cudaMemcpy(pool->d_bases, pool->base.data(), desc->regions * sizeof(unsigned long long), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    int32_t rc = cuda_fail(ctx, e, "pool base upload");
+    cudaFree(pool->d_bases);
+    delete pool;
+    return rc;
+  }
+  *out = pool;
+  return KVX_OK;
+}
+
+int32_t kvx_pool_release(kvx_pool* pool) {
+  if (!pool) return KVX_EINVAL;
+  DeviceGuard guard(pool->ctx->device);
+  for (void* p : pool->imported_ptrs) unmap_ptr(pool->ctx, p);
+  cudaFree(pool->d_bases);
+  (void)cudaGetLastError();
+  delete pool;
+  return KVX_OK;
+}
+
+int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes) {
+  if (!pool || !bytes) return KVX_EINVAL;
+  *bytes = pool->chunk_bytes;
+  return KVX_OK;
+}
+
+int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) {
+  if (!pool || !len) return KVX_EINVAL;
+  const size_t need = sizeof(PoolRecordHeader) + pool->base.size() * sizeof(MemRecord);
+  if (!buf || *len < need) {
+    *len = need;
+    return KVX_ERANGE;
+  }
+  PoolRecordHeader h{};
+  const kvx_pool_desc& d = pool->desc;
+  h.magic = kPoolMagic; h.regions = d.regions; h.block_tokens = d.block_tokens; h.heads = d.heads;
+  h.head_dim = d.head_dim; h.elem_bytes = d.elem_bytes; h.layout = d.layout; h.tp_rank = d.tp_rank;
+  h.tp_size = d.tp_size; h.num_blocks = d.num_blocks; h.block_stride = d.block_stride;
+  memcpy(buf, &h, sizeof(h));
+  char* w = static_cast<char*>(buf) + sizeof(h);
+  const uint64_t span = (d.num_blocks - 1) * d.block_stride + pool->chunk_bytes;
+  for (size_t r = 0; r < pool->base.size(); ++r) {
+    MemRecord rec;
+    int32_t rc = export_record(pool->ctx, pool->base[r], span, &rec);
+    if (rc) return rc;
+    memcpy(w + r * sizeof(MemRecord), &rec, sizeof(rec));
+  }
+  *len = need;
+  return KVX_OK;
+}
+
+int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out) {
+  if (!ctx || !buf || !out || len < sizeof(PoolRecordHeader)) return KVX_EINVAL;
+  PoolRecordHeader h;
+  memcpy(&h, buf, sizeof(h));
+  if (h.magic != kPoolMagic) return KVX_EINVAL;
+  if (len < sizeof(h) + static_cast<size_t>(h.regions) * sizeof(MemRecord)) return KVX_EINVAL;
+  std::vector<void*> bases(h.regions, nullptr);
+  const char* r = static_cast<const char*>(buf) + sizeof(h);
+  int32_t rc = KVX_OK;
+  uint32_t done = 0;
+  for (; done < h.regions; ++done) {
+    MemRecord rec;
+    memcpy(&rec, r + done * sizeof(MemRecord), sizeof(rec));
+    rc = import_record(ctx, &rec, &bases[done]);
+    if (rc) break;
+  }
+  if (rc) {
+    for (uint32_t i = 0; i < done; ++i) unmap_ptr(ctx, bases[i]);
+    return rc;
+  }
+  kvx_pool_desc d{};
+  d.struct_size = sizeof(d); d.regions = h.regions; d.block_tokens = h.block_tokens; d.heads = h.heads;
+  d.head_dim = h.head_dim; d.elem_bytes = h.elem_bytes; d.layout = h.layout; d.tp_rank = h.tp_rank;
+  d.tp_size = h.tp_size; d.num_blocks = h.num_blocks; d.block_stride = h.block_stride; d.base = bases.data();
+  kvx_pool* pool = nullptr;
+  rc = kvx_pool_register(ctx, &d, &pool);
+  if (rc) {
+    for (void* p : bases) unmap_ptr(ctx, p);
+    return rc;
+  }
+  pool->imported_ptrs = bases;
+  *out = pool;
+  return KVX_OK;
+}
+
+int32_t kvx_ctx_flags(kvx_ctx* ctx, uint64_t** flags, uint32_t* count) {
+  if (!ctx || !flags || !count) return KVX_EINVAL;
+  *flags = ctx->d_flags;
+  *count = kNumFlags;
+  return KVX_OK;
+}
+
+int32_t kvx_flag_reset(kvx_ctx* ctx, uint64_t* flag, uint64_t value, void* stream) {
+  if (!ctx || !flag) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  KVX_CUDA(ctx, cudaMemcpyAsync(flag, &value, sizeof(value), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return KVX_OK;
+}
+
+int32_t kvx_flag_wait(kvx_ctx* ctx, const uint64_t* flag, uint64_t value, uint32_t timeout_ms, void* stream) {
+  if (!ctx || !flag) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  const unsigned long long ns = static_cast<unsigned long long>(timeout_ms ? timeout_ms : 1000u) * 1000000ull;
+  kvx::kvx_flag_wait_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const unsigned long long*>(flag), value, ns, ctx->d_status);
+  KVX_CUDA(ctx, cudaGetLastError());
+  ctx->launches++;
+  return KVX_OK;
+}
+
+int32_t kvx_flag_poll(kvx_ctx* ctx, const uint64_t* flag, uint64_t value) {
+  if (!ctx || !flag) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  uint64_t cur = 0;
+  KVX_CUDA(ctx, cudaMemcpyAsync(&cur, flag, sizeof(cur), cudaMemcpyDeviceToHost, ctx->aux));
+  KVX_CUDA(ctx, cudaStreamSynchronize(ctx->aux));
+  return cur >= value ? KVX_OK : KVX_ENOTREADY;
+}
+
+int32_t kvx_ctx_check(kvx_ctx* ctx) {
+  if (!ctx) return KVX_EINVAL;
+  DeviceGuard guard(ctx->device);
+  unsigned st = 0;
+  KVX_CUDA(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, ctx->aux));
+  KVX_CUDA(ctx, cudaStreamSynchronize(ctx->aux));
+  if (st != 0) {
+    KVX_CUDA(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(unsigned), ctx->aux));
+    KVX_CUDA(ctx, cudaStreamSynchronize(ctx->aux));
+  }
+  if (st & kvx::kStatusWaitTimeout) return KVX_ETIMEOUT;
+  if (st & kvx::kStatusBadBlockId) return KVX_ERANGE;
+  return KVX_OK;
+}
+
+int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, uint32_t n, void* staging,
+                   const kvx_xform* xf, void* stream) {
+  if (!ctx || !src) return KVX_EINVAL;
+  if (n == 0) return KVX_OK;
+  if (!d_table || !staging || reinterpret_cast<uintptr_t>(staging) % 16 != 0) return KVX_EINVAL;
+  uint32_t so, dof, hc, sl;
+  int32_t rc = resolve_xform(&src->desc, nullptr, xf, &so, &dof, &hc, &sl, src->desc.layout);
+  if (rc) return rc;
+  const kvx_pool_desc& d = src->desc;
+  LaunchSpec ls;
+  ls.src = paged_side(src, d_table);
+  const uint64_t stage_chunk = static_cast<uint64_t>(d.block_tokens) * hc * d.head_dim * d.elem_bytes;
+  ls.dst = contiguous_side(staging, stage_chunk);
+  ls.n = n; ls.regions = d.regions;
+  ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
+  ls.sg = ChunkGeom{d.layout, d.heads, so};
+  ls.dg = ChunkGeom{sl, hc, 0};
+  return launch_xfer(ctx, ls, &src->base, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, const int32_t* d_table, uint32_t n,
+                    const kvx_xform* xf, void* stream) {
+  if (!ctx || !dst) return KVX_EINVAL;
+  if (n == 0) return KVX_OK;
+  if (!d_table || !staging || reinterpret_cast<uintptr_t>(staging) % 16 != 0) return KVX_EINVAL;
+  uint32_t so, dof, hc, sl;
+  int32_t rc = resolve_xform(nullptr, &dst->desc, xf, &so, &dof, &hc, &sl, dst->desc.layout);
+  if (rc) return rc;
+  const kvx_pool_desc& d = dst->desc;
+  LaunchSpec ls;
+  const uint64_t stage_chunk = static_cast<uint64_t>(d.block_tokens) * hc * d.head_dim * d.elem_bytes;
+  ls.src = contiguous_side(staging, stage_chunk);
+  ls.dst = paged_side(dst, d_table);
+  ls.n = n; ls.regions = d.regions;
+  ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
+  ls.sg = ChunkGeom{sl, hc, 0};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof};
+  return launch_xfer(ctx, ls, nullptr, &dst->base, static_cast<cudaStream_t>(stream));
+}
+
+int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint64_t* flag, uint64_t flag_val,
+                 void* stream) {
+  if (!ctx) return KVX_EINVAL;
+  if (bytes != 0 && (!src || !dst)) return KVX_EINVAL;
+  if (bytes % 16 != 0 || reinterpret_cast<uintptr_t>(src) % 16 != 0 || reinterpret_cast<uintptr_t>(dst) % 16 != 0)
+    return KVX_EINVAL;
+  LaunchSpec ls;
+  ls.src = contiguous_side(src, 0);
+  ls.dst = contiguous_side(dst, 0);
+  ls.copy_mode = true;
+  ls.copy_bytes = bytes;
+  ls.flag = flag;
+  ls.flag_val = flag_val;
+  if (bytes == 0) {
+    if (flag) return kvx_flag_reset(ctx, flag, flag_val, stream);
+    return KVX_OK;
+  }
+  return launch_xfer(ctx, ls, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table, const kvx_pool* dst,
+                          const int32_t* d_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag,
+                          uint64_t flag_val, void* stream) {
+  if (!ctx || !src || !dst) return KVX_EINVAL;
+  if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
+  if (n != 0 && (!d_src_table || !d_dst_table)) return KVX_EINVAL;
+  uint32_t so, dof, hc, sl;
+  int32_t rc = resolve_xform(&src->desc, &dst->desc, xf, &so, &dof, &hc, &sl, src->desc.layout);
+  if (rc) return rc;
+  const kvx_pool_desc& s = src->desc;
+  const kvx_pool_desc& d = dst->desc;
+  LaunchSpec ls;
+  ls.src = paged_side(src, d_src_table);
+  ls.dst = paged_side(dst, d_dst_table);
+  ls.n = n; ls.regions = s.regions;
+  ls.N = s.block_tokens; ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
+  ls.sg = ChunkGeom{s.layout, s.heads, so};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof};
+  ls.flag = flag;
+  ls.flag_val = flag_val;
+  return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
+}
+
+int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table, const kvx_pool* dst,
+                         const int32_t* h_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag,
+                         uint64_t flag_val, uint64_t* h_done, void* stream) {
+  if (!ctx || !src || !dst) return KVX_EINVAL;
+  if (n > KVX_MAX_HOST_TABLE) return KVX_ERANGE;
+  if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DeviceGuard guard(ctx->device);
+  // The peer may own the destination blocks: ids are validated here against each pool's size so a
+  // bad list never reaches the kernel (the kernel re-checks device-resident tables itself).
+  for (uint32_t i = 0; i < n; ++i) {
+    if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->desc.num_blocks) return KVX_ERANGE;
+    if (h_dst_table[i] < 0 || static_cast<uint64_t>(h_dst_table[i]) >= dst->desc.num_blocks) return KVX_ERANGE;
+  }
+  int* d_src = nullptr;
+  int* d_dst = nullptr;
+  if (n != 0) {
+    if (ctx->table_cursor + 2ull * n > kTableRing) ctx->table_cursor = 0;
+    d_src = ctx->d_table_ring + ctx->table_cursor;
+    d_dst = d_src + n;
+    ctx->table_cursor += 2 * n;
+    KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, n * sizeof(int), cudaMemcpyHostToDevice, st));
+    KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, n * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  uint64_t* f = flag ? flag : ctx->d_flags + (kNumFlags - 1);
+  int32_t rc = kvx_handoff_fused(ctx, src, d_src, dst, d_dst, n, xf, f, flag_val, stream);
+  if (rc) return rc;
+  if (h_done) {
+    // A peer flag is readable through the same mapping the kernel wrote it through.
+    KVX_CUDA(ctx, cudaMemcpyAsync(h_done, f, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  }
+  return KVX_OK;
+}
+
+}  // extern "C"

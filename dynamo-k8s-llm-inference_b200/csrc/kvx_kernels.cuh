@@ -1,0 +1,434 @@
+// kvx_kernels.cuh — sm_100a device code of the KV handoff path.
+//
+// One generic "transfer" (xfer) moves work items from a source side to a destination side.  A work
+// item is a PIECE of one CHUNK; a chunk is one block of one region (K or V of one layer) of one
+// rank: N tokens x H heads x D x E bytes.  Each side is either PAGED (address = region base +
+// block id x stride, the block id looked up in the request's block table) or CONTIGUOUS (a staging
+// image [regions][n][chunk]).  gather = paged→contiguous, scatter = contiguous→paged, fused
+// handoff = paged→paged (the destination may be a peer GPU's memory mapped over NVLink), copy =
+// contiguous→contiguous.  Layout transform and TP head slicing are expressed as run descriptors
+// (see XferParams); the kernels contain no arithmetic on the payload.
+//
+// Two engines:
+//   kvx_xfer_tma_kernel — persistent CTAs, one producer warp feeding an mbarrier ring of
+//     shared-memory stages with cp.async.bulk (TMA bulk copy), consumer warps draining each stage
+//     either with one cp.async.bulk store per destination run or with 16/32-byte vector stores.
+//   kvx_xfer_ldg_kernel — persistent CTAs, 16/32-byte vector loads straight to vector stores,
+//     offsets hoisted into registers.
+// Both resolve block tables a warp at a time (32 items per lookup, broadcast with shuffles).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace kvx {
+
+constexpr int kMaxStages = 8;
+constexpr unsigned kStatusBadBlockId = 1u;
+constexpr unsigned kStatusWaitTimeout = 2u;
+
+struct XferSide {
+  const unsigned long long* bases;  // paged: device array [regions] of region base addresses; null = contiguous
+  const int* table;                 // paged: device array [n] of block ids
+  unsigned long long base0;         // contiguous: base address of the image
+  unsigned long long block_stride;  // paged: bytes per block id; contiguous: bytes per (region, i) chunk
+  unsigned long long num_blocks;    // paged: ids must be < num_blocks
+  unsigned int slice_off;           // byte offset of the moved slice inside a chunk
+  unsigned int piece_stride;        // bytes between consecutive pieces of one chunk
+};
+
+struct XferParams {
+  XferSide src, dst;
+  unsigned int total_items;  // regions * n * ppc
+  unsigned int n, regions, ppc;
+  unsigned int piece_bytes;  // bytes moved per item
+  unsigned int tail_bytes;   // bytes of the very last item (copy mode), 0 = piece_bytes
+  // Source runs of one piece: run x (< s_runs) starts at x * s_stride, s_run_bytes long; the piece
+  // image in shared memory / in item order is the runs back to back.
+  unsigned int s_runs, s_run_bytes, s_stride;
+  // Destination runs of one piece: run x (< d_runs) covers image bytes [x*d_run_bytes, +d_run_bytes)
+  // and lands at (x / d_n1) * d_stride_a + (x % d_n1) * d_stride_b.
+  unsigned int d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b;
+  unsigned int stages, stage_bytes;
+  unsigned int l2_hint;
+  unsigned long long* flag;  // completion flag (local or peer memory) or null
+  unsigned long long flag_val;
+  unsigned int* done_counter;  // scratch: CTAs finished (zero on entry, zero again on exit)
+  unsigned int* status;        // scratch: sticky error bits
+};
+
+// ----------------------------------------------------------------------------------------------
+// PTX wrappers
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a pipeline bug must trap, not hang the GPU.
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
+    if (spins > (1u << 26)) __trap();
+  }
+}
+__device__ __forceinline__ unsigned long long l2_policy_evict_first() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+// TMA bulk copy global → shared, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, unsigned long long gsrc, uint32_t bytes,
+                                         unsigned long long* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_hint(void* smem_dst, unsigned long long gsrc, uint32_t bytes,
+                                              unsigned long long* bar, unsigned long long pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], "
+      "%4;" ::"r"(smem_u32(smem_dst)),
+      "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+      : "memory");
+}
+// TMA bulk copy shared → global (local HBM or a peer's, the address decides).
+__device__ __forceinline__ void bulk_s2g(unsigned long long gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int VEC>
+struct Vec;
+template <>
+struct Vec<16> {
+  uint32_t v[4];
+};
+template <>
+struct Vec<32> {
+  uint32_t v[8];
+};
+
+__device__ __forceinline__ void ldg_stream(Vec<16>& r, unsigned long long a) {
+  asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3])
+               : "l"(a));
+}
+__device__ __forceinline__ void ldg_stream(Vec<32>& r, unsigned long long a) {
+  asm volatile("ld.global.nc.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.v[0]), "=r"(r.v[1]), "=r"(r.v[2]), "=r"(r.v[3]), "=r"(r.v[4]), "=r"(r.v[5]),
+                 "=r"(r.v[6]), "=r"(r.v[7])
+               : "l"(a));
+}
+__device__ __forceinline__ void stg_stream(unsigned long long a, const Vec<16>& r) {
+  asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(a), "r"(r.v[0]), "r"(r.v[1]),
+               "r"(r.v[2]), "r"(r.v[3])
+               : "memory");
+}
+__device__ __forceinline__ void stg_stream(unsigned long long a, const Vec<32>& r) {
+  asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(a), "r"(r.v[0]),
+               "r"(r.v[1]), "r"(r.v[2]), "r"(r.v[3]), "r"(r.v[4]), "r"(r.v[5]), "r"(r.v[6]), "r"(r.v[7])
+               : "memory");
+}
+__device__ __forceinline__ void lds_vec(Vec<16>& r, const unsigned char* s) {
+  const uint4 t = *reinterpret_cast<const uint4*>(s);
+  r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+}
+__device__ __forceinline__ void lds_vec(Vec<32>& r, const unsigned char* s) {
+  const uint4 t0 = *reinterpret_cast<const uint4*>(s);
+  const uint4 t1 = *reinterpret_cast<const uint4*>(s + 16);
+  r.v[0] = t0.x; r.v[1] = t0.y; r.v[2] = t0.z; r.v[3] = t0.w;
+  r.v[4] = t1.x; r.v[5] = t1.y; r.v[6] = t1.z; r.v[7] = t1.w;
+}
+
+// ----------------------------------------------------------------------------------------------
+// Item decode: item w → (piece, i, region) → source / destination byte address.  A block id outside
+// [0, num_blocks) yields bytes == 0 (the item is skipped) and raises kStatusBadBlockId.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long side_addr(const XferSide& s, unsigned r, unsigned i, unsigned piece,
+                                                        unsigned n, bool& ok) {
+  unsigned long long a;
+  if (s.bases != nullptr) {
+    const int id = s.table ? __ldg(s.table + i) : static_cast<int>(i);
+    if (id < 0 || static_cast<unsigned long long>(id) >= s.num_blocks) {
+      ok = false;
+      return 0;
+    }
+    a = __ldg(s.bases + r) + static_cast<unsigned long long>(id) * s.block_stride;
+  } else {
+    a = s.base0 + (static_cast<unsigned long long>(r) * n + i) * s.block_stride;
+  }
+  return a + s.slice_off + static_cast<unsigned long long>(piece) * s.piece_stride;
+}
+
+__device__ __forceinline__ void decode_item(const XferParams& p, unsigned w, unsigned long long& sa,
+                                            unsigned long long& da, unsigned& bytes) {
+  const unsigned piece = w % p.ppc;
+  const unsigned c = w / p.ppc;
+  const unsigned i = c % p.n;
+  const unsigned r = c / p.n;
+  bool ok = true;
+  sa = side_addr(p.src, r, i, piece, p.n, ok);
+  da = side_addr(p.dst, r, i, piece, p.n, ok);
+  bytes = (p.tail_bytes != 0 && w == p.total_items - 1) ? p.tail_bytes : p.piece_bytes;
+  if (!ok) {
+    bytes = 0;
+    atomicOr(p.status, kStatusBadBlockId);
+  }
+}
+
+__device__ __forceinline__ unsigned dst_run_offset(const XferParams& p, unsigned x) {
+  return (x / p.d_n1) * p.d_stride_a + (x % p.d_n1) * p.d_stride_b;
+}
+
+// Completion: every CTA publishes its stores system-wide, the last one to finish release-stores the
+// flag (H6) and re-zeroes the counter for the next launch that gets this counter slot.
+__device__ __forceinline__ void finish_and_flag(const XferParams& p) {
+  if (p.flag == nullptr) return;
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(p.done_counter, 1u);
+    if (prev == gridDim.x - 1) {
+      __threadfence_system();
+      *p.done_counter = 0u;
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+    }
+  }
+}
+
+// ----------------------------------------------------------------------------------------------
+// TMA engine.  blockDim.x = 32 * (1 + consumer warps); warp 0 produces.
+// STORE: 16 / 32 = vector stores of that many bytes by the consumer threads; 0 = bulk stores.
+// ----------------------------------------------------------------------------------------------
+template <int STORE, int KMAX>
+__global__ void kvx_xfer_tma_kernel(const XferParams p) {
+  extern __shared__ __align__(1024) unsigned char stage_mem[];
+  __shared__ __align__(8) unsigned long long full_bar[kMaxStages];
+  __shared__ __align__(8) unsigned long long empty_bar[kMaxStages];
+  __shared__ unsigned long long meta_dst[kMaxStages];
+  __shared__ unsigned int meta_bytes[kMaxStages];
+
+  const unsigned tid = threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const unsigned warp = tid >> 5;
+  const unsigned cons_warps = (blockDim.x >> 5) - 1u;
+  const unsigned S = p.stages;
+
+  if (tid == 0) {
+    for (unsigned s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1u);
+      mbar_init(&empty_bar[s], cons_warps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  const unsigned bid = blockIdx.x;
+  const unsigned grid = gridDim.x;
+  const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+
+  if (warp == 0) {
+    // ------------------------------ producer ------------------------------
+    const unsigned long long pol = p.l2_hint ? l2_policy_evict_first() : 0ull;
+    for (unsigned base = 0; base < my_items; base += 32u) {
+      unsigned long long sa = 0, da = 0;
+      unsigned bytes = 0;
+      if (base + lane < my_items) decode_item(p, bid + (base + lane) * grid, sa, da, bytes);
+      const unsigned cnt = min(32u, my_items - base);
+      for (unsigned j = 0; j < cnt; ++j) {
+        const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
+        const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
+        const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
+        const unsigned it = base + j;
+        const unsigned s = it % S;
+        const unsigned round = it / S;
+        mbar_wait(&empty_bar[s], (round & 1u) ^ 1u);
+        unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+        if (lane == 0) {
+          meta_dst[s] = dst;
+          meta_bytes[s] = nbytes;
+          mbar_arrive_expect_tx(&full_bar[s], nbytes);
+        }
+        __syncwarp();
+        if (nbytes != 0) {
+          if (p.s_runs == 1u) {
+            if (lane == 0) {
+              if (p.l2_hint) bulk_g2s_hint(stage, src, nbytes, &full_bar[s], pol);
+              else bulk_g2s(stage, src, nbytes, &full_bar[s]);
+            }
+          } else {
+            for (unsigned x = lane; x < p.s_runs; x += 32u) {
+              if (p.l2_hint)
+                bulk_g2s_hint(stage + x * p.s_run_bytes, src + static_cast<unsigned long long>(x) * p.s_stride,
+                              p.s_run_bytes, &full_bar[s], pol);
+              else
+                bulk_g2s(stage + x * p.s_run_bytes, src + static_cast<unsigned long long>(x) * p.s_stride,
+                         p.s_run_bytes, &full_bar[s]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ------------------------------ consumers -----------------------------
+    const unsigned ctid = tid - 32u;
+    const unsigned T = blockDim.x - 32u;
+    if constexpr (STORE == 0) {
+      // One cp.async.bulk store per destination run, runs spread over the consumer threads.
+      // A stage is handed back one item late so that two stores stay in flight per thread.
+      unsigned prev_stage = 0;
+      bool have_prev = false;
+      for (unsigned it = 0; it < my_items; ++it) {
+        const unsigned s = it % S;
+        mbar_wait(&full_bar[s], (it / S) & 1u);
+        const unsigned long long dst = meta_dst[s];
+        const unsigned nbytes = meta_bytes[s];
+        const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+        if (nbytes != 0) {
+          if (p.d_runs == 1u) {
+            if (ctid == 0) bulk_s2g(dst, stage, nbytes);
+          } else {
+            for (unsigned x = ctid; x < p.d_runs; x += T)
+              bulk_s2g(dst + dst_run_offset(p, x), stage + x * p.d_run_bytes, p.d_run_bytes);
+          }
+        }
+        bulk_commit();
+        if (have_prev) {
+          bulk_wait_read<1>();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty_bar[prev_stage]);
+        }
+        prev_stage = s;
+        have_prev = true;
+      }
+      bulk_wait<0>();  // all bytes written before the completion fence
+    } else {
+      constexpr int VEC = STORE;
+      // Destination offsets of this thread's units are the same for every piece: hoist them.
+      unsigned doff[KMAX];
+      const unsigned upr = p.d_run_bytes / VEC;  // units per destination run
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k) {
+        const unsigned u = ctid + k * T;
+        const unsigned x = u / upr;
+        doff[k] = dst_run_offset(p, x) + (u % upr) * VEC;
+      }
+      for (unsigned it = 0; it < my_items; ++it) {
+        const unsigned s = it % S;
+        mbar_wait(&full_bar[s], (it / S) & 1u);
+        const unsigned long long dst = meta_dst[s];
+        const unsigned units = meta_bytes[s] / VEC;
+        const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+        Vec<VEC> v[KMAX];
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+          const unsigned u = ctid + k * T;
+          if (u < units) lds_vec(v[k], stage + static_cast<size_t>(u) * VEC);
+        }
+#pragma unroll
+        for (int k = 0; k < KMAX; ++k) {
+          const unsigned u = ctid + k * T;
+          if (u < units) stg_stream(dst + doff[k], v[k]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[s]);
+      }
+    }
+  }
+  finish_and_flag(p);
+}
+
+// ----------------------------------------------------------------------------------------------
+// LDG engine: no shared memory; each thread owns KMAX vector units of every piece.
+// ----------------------------------------------------------------------------------------------
+template <int VEC, int KMAX>
+__global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
+  const unsigned tid = threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const unsigned T = blockDim.x;
+  unsigned soff[KMAX], doff[KMAX];
+  {
+    const unsigned supr = p.s_run_bytes / VEC;
+    const unsigned dupr = p.d_run_bytes / VEC;
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      const unsigned u = tid + k * T;
+      soff[k] = (u / supr) * p.s_stride + (u % supr) * VEC;
+      doff[k] = dst_run_offset(p, u / dupr) + (u % dupr) * VEC;
+    }
+  }
+  const unsigned bid = blockIdx.x;
+  const unsigned grid = gridDim.x;
+  const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+  for (unsigned base = 0; base < my_items; base += 32u) {
+    unsigned long long sa = 0, da = 0;
+    unsigned bytes = 0;
+    if (base + lane < my_items) decode_item(p, bid + (base + lane) * grid, sa, da, bytes);
+    const unsigned cnt = min(32u, my_items - base);
+    for (unsigned j = 0; j < cnt; ++j) {
+      const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
+      const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
+      const unsigned units = __shfl_sync(0xffffffffu, bytes, j) / VEC;
+      Vec<VEC> v[KMAX];
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (tid + k * T < units) ldg_stream(v[k], src + soff[k]);
+#pragma unroll
+      for (int k = 0; k < KMAX; ++k)
+        if (tid + k * T < units) stg_stream(dst + doff[k], v[k]);
+    }
+  }
+  finish_and_flag(p);
+}
+
+// Stream-ordered, bounded wait on a completion flag written by another GPU.
+__global__ void kvx_flag_wait_kernel(const unsigned long long* flag, unsigned long long value,
+                                     unsigned long long timeout_ns, unsigned int* status) {
+  unsigned long long t0, now, cur;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(cur) : "l"(flag) : "memory");
+    if (cur >= value) return;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    if (now - t0 > timeout_ns) {
+      atomicOr(status, kStatusWaitTimeout);
+      return;
+    }
+    __nanosleep(256);
+  }
+}
+
+}  // namespace kvx

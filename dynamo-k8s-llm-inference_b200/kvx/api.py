@@ -1,0 +1,231 @@
+"""Thin object layer over the C ABI: Context, Pool, and the transfer verbs.
+
+Mirrors the verbs the reference's images use on this path (vLLM NIXL connector, cited in
+include/kvx.h): register_kv_caches → Context.register_pool, get_agent_metadata/add_remote_agent →
+Pool.export / Context.import_pool, make_prepped_xfer+transfer → gather/copy/scatter/handoff,
+check_xfer_state → flag_poll / flag_wait.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+from . import _lib
+from ._lib import PoolDesc, XformC, c_i32, c_i64, c_sz, c_u32, c_u64, c_vp
+
+NHD, HND = 0, 1
+OPT = {"engine": 0, "stages": 1, "stage_bytes": 2, "ctas_per_sm": 3, "store_mode": 4, "vec_bytes": 5,
+       "consumer_warps": 6, "l2_hint": 7}
+ENGINE = {"auto": 0, "ldg": 1, "tma": 2}
+OK, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED, ETIMEOUT, ERANGE, EIPC, ENOTREADY = 0, -1, -2, -3, -4, -5, -6, -7, -8
+
+
+class KvxError(RuntimeError):
+    def __init__(self, code: int, where: str, detail: str = ""):
+        self.code = code
+        msg = _lib.load().kvx_strerror(code).decode()
+        super().__init__(f"{where}: {msg} ({code})" + (f": {detail}" if detail else ""))
+
+
+@dataclass
+class Xform:
+    """kvx_xform: head slice moved by one edge and the staging row order."""
+
+    src_head_off: int = 0
+    dst_head_off: int = 0
+    heads: int = 0
+    stage_layout: int = NHD
+
+    def c(self) -> XformC:
+        return XformC(self.src_head_off, self.dst_head_off, self.heads, self.stage_layout)
+
+
+def _ptr(x) -> Optional[int]:
+    """Device/host address from an int, a torch tensor, a numpy array or None."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if hasattr(x, "data_ptr"):
+        return x.data_ptr()
+    if hasattr(x, "ctypes"):
+        return x.ctypes.data
+    raise TypeError(type(x))
+
+
+def _stream(stream) -> Optional[int]:
+    if stream is None:
+        return None
+    if isinstance(stream, int):
+        return stream or None
+    return stream.cuda_stream or None  # torch.cuda.Stream
+
+
+class Pool:
+    def __init__(self, ctx: "Context", handle: int, *, regions, block_tokens, heads, head_dim, elem_bytes, layout,
+                 num_blocks, imported=False):
+        self.ctx, self.handle = ctx, handle
+        self.regions, self.block_tokens, self.heads = regions, block_tokens, heads
+        self.head_dim, self.elem_bytes, self.layout, self.num_blocks = head_dim, elem_bytes, layout, num_blocks
+        self.imported = imported
+
+    @property
+    def chunk_bytes(self) -> int:
+        out = c_u64()
+        self.ctx._check(self.ctx.lib.kvx_pool_chunk_bytes(self.handle, ctypes.byref(out)), "kvx_pool_chunk_bytes")
+        return out.value
+
+    def export(self) -> bytes:
+        need = c_sz(0)
+        self.ctx.lib.kvx_pool_export(self.handle, None, ctypes.byref(need))
+        buf = ctypes.create_string_buffer(need.value)
+        self.ctx._check(self.ctx.lib.kvx_pool_export(self.handle, buf, ctypes.byref(need)), "kvx_pool_export")
+        return buf.raw[: need.value]
+
+    def release(self) -> None:
+        if self.handle:
+            self.ctx.lib.kvx_pool_release(self.handle)
+            self.handle = None
+
+
+class Context:
+    """One worker's transfer context on one GPU (kvx_ctx)."""
+
+    def __init__(self, device: int = 0, **options):
+        self.lib = _lib.load()
+        h = c_vp()
+        rc = self.lib.kvx_ctx_create(device, ctypes.byref(h))
+        if rc != OK:
+            raise KvxError(rc, "kvx_ctx_create", "a CUDA device is required; kvx has no CPU fallback")
+        self.handle, self.device = h.value, device
+        for k, v in options.items():
+            self.set_option(k, v)
+
+    # -- plumbing -------------------------------------------------------------------------------
+    def _check(self, rc: int, where: str) -> None:
+        if rc != OK:
+            raise KvxError(rc, where, self.lib.kvx_last_error(self.handle).decode() if rc == ECUDA else "")
+
+    def close(self) -> None:
+        if self.handle:
+            self.lib.kvx_ctx_destroy(self.handle)
+            self.handle = None
+
+    def set_option(self, name: str, value) -> None:
+        if name == "engine" and isinstance(value, str):
+            value = ENGINE[value]
+        self._check(self.lib.kvx_ctx_set_option(self.handle, OPT[name], int(value)), f"kvx_ctx_set_option({name})")
+
+    def get_option(self, name: str) -> int:
+        out = c_i64()
+        self._check(self.lib.kvx_ctx_get_option(self.handle, OPT[name], ctypes.byref(out)), "kvx_ctx_get_option")
+        return out.value
+
+    @property
+    def launch_count(self) -> int:
+        out = c_u64()
+        self._check(self.lib.kvx_ctx_launch_count(self.handle, ctypes.byref(out)), "kvx_ctx_launch_count")
+        return out.value
+
+    @property
+    def sm_count(self) -> int:
+        out = c_i32()
+        self._check(self.lib.kvx_ctx_sm_count(self.handle, ctypes.byref(out)), "kvx_ctx_sm_count")
+        return out.value
+
+    def check(self) -> None:
+        self._check(self.lib.kvx_ctx_check(self.handle), "kvx_ctx_check")
+
+    # -- memory ---------------------------------------------------------------------------------
+    def mem_alloc(self, nbytes: int) -> int:
+        out = c_vp()
+        self._check(self.lib.kvx_mem_alloc(self.handle, nbytes, ctypes.byref(out)), "kvx_mem_alloc")
+        return out.value
+
+    def mem_free(self, ptr: int) -> None:
+        self._check(self.lib.kvx_mem_free(self.handle, ptr), "kvx_mem_free")
+
+    def mem_export(self, ptr, nbytes: int) -> bytes:
+        need = c_sz(0)
+        self.lib.kvx_mem_export(self.handle, _ptr(ptr), nbytes, None, ctypes.byref(need))
+        buf = ctypes.create_string_buffer(need.value)
+        self._check(self.lib.kvx_mem_export(self.handle, _ptr(ptr), nbytes, buf, ctypes.byref(need)), "kvx_mem_export")
+        return buf.raw[: need.value]
+
+    def mem_import(self, blob: bytes) -> int:
+        out = c_vp()
+        self._check(self.lib.kvx_mem_import(self.handle, blob, len(blob), ctypes.byref(out)), "kvx_mem_import")
+        return out.value
+
+    def mem_unmap(self, ptr: int) -> None:
+        self._check(self.lib.kvx_mem_unmap(self.handle, ptr), "kvx_mem_unmap")
+
+    # -- pools ----------------------------------------------------------------------------------
+    def register_pool(self, bases: Sequence[int], *, num_blocks: int, heads: int, head_dim: int, layout: int,
+                      block_tokens: int = 16, elem_bytes: int = 2, block_stride: int = 0, tp_rank: int = 0,
+                      tp_size: int = 1) -> Pool:
+        arr = (c_vp * len(bases))(*[int(b) for b in bases])
+        d = PoolDesc(ctypes.sizeof(PoolDesc), len(bases), block_tokens, heads, head_dim, elem_bytes, layout, tp_rank,
+                     tp_size, 0, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
+        h = c_vp()
+        self._check(self.lib.kvx_pool_register(self.handle, ctypes.byref(d), ctypes.byref(h)), "kvx_pool_register")
+        return Pool(self, h.value, regions=len(bases), block_tokens=block_tokens, heads=heads, head_dim=head_dim,
+                    elem_bytes=elem_bytes, layout=layout, num_blocks=num_blocks)
+
+    def import_pool(self, blob: bytes) -> Pool:
+        h = c_vp()
+        self._check(self.lib.kvx_pool_import(self.handle, blob, len(blob), ctypes.byref(h)), "kvx_pool_import")
+        import struct
+
+        (_, regions, N, H, D, E, layout, _, _, _, nb, _) = struct.unpack_from("<10I2Q", blob, 0)
+        return Pool(self, h.value, regions=regions, block_tokens=N, heads=H, head_dim=D, elem_bytes=E, layout=layout,
+                    num_blocks=nb, imported=True)
+
+    # -- flags ----------------------------------------------------------------------------------
+    def flags(self):
+        ptr, cnt = c_vp(), c_u32()
+        self._check(self.lib.kvx_ctx_flags(self.handle, ctypes.byref(ptr), ctypes.byref(cnt)), "kvx_ctx_flags")
+        return ptr.value, cnt.value
+
+    def flag_reset(self, flag: int, value: int = 0, stream=None) -> None:
+        self._check(self.lib.kvx_flag_reset(self.handle, flag, value, _stream(stream)), "kvx_flag_reset")
+
+    def flag_wait(self, flag: int, value: int, timeout_ms: int = 2000, stream=None) -> None:
+        self._check(self.lib.kvx_flag_wait(self.handle, flag, value, timeout_ms, _stream(stream)), "kvx_flag_wait")
+
+    def flag_poll(self, flag: int, value: int) -> bool:
+        rc = self.lib.kvx_flag_poll(self.handle, flag, value)
+        if rc == ENOTREADY:
+            return False
+        self._check(rc, "kvx_flag_poll")
+        return True
+
+    # -- transfers ------------------------------------------------------------------------------
+    def gather(self, src: Pool, d_table, n: int, staging, xf: Optional[Xform] = None, stream=None) -> None:
+        x = xf.c() if xf else None
+        self._check(self.lib.kvx_gather(self.handle, src.handle, _ptr(d_table), n, _ptr(staging),
+                                        ctypes.byref(x) if x else None, _stream(stream)), "kvx_gather")
+
+    def scatter(self, staging, dst: Pool, d_table, n: int, xf: Optional[Xform] = None, stream=None) -> None:
+        x = xf.c() if xf else None
+        self._check(self.lib.kvx_scatter(self.handle, _ptr(staging), dst.handle, _ptr(d_table), n,
+                                         ctypes.byref(x) if x else None, _stream(stream)), "kvx_scatter")
+
+    def copy(self, src, dst, nbytes: int, flag: Optional[int] = None, flag_val: int = 0, stream=None) -> None:
+        self._check(self.lib.kvx_copy(self.handle, _ptr(src), _ptr(dst), nbytes, flag, flag_val, _stream(stream)),
+                    "kvx_copy")
+
+    def handoff_fused(self, src: Pool, d_src_table, dst: Pool, d_dst_table, n: int, xf: Optional[Xform] = None,
+                      flag: Optional[int] = None, flag_val: int = 0, stream=None) -> None:
+        x = xf.c() if xf else None
+        self._check(self.lib.kvx_handoff_fused(self.handle, src.handle, _ptr(d_src_table), dst.handle,
+                                               _ptr(d_dst_table), n, ctypes.byref(x) if x else None, flag, flag_val,
+                                               _stream(stream)), "kvx_handoff_fused")
+
+    def handoff_host(self, src: Pool, h_src_table, dst: Pool, h_dst_table, n: int, xf: Optional[Xform] = None,
+                     flag: Optional[int] = None, flag_val: int = 1, h_done=None, stream=None) -> None:
+        x = xf.c() if xf else None
+        self._check(self.lib.kvx_handoff_host(self.handle, src.handle, _ptr(h_src_table), dst.handle,
+                                              _ptr(h_dst_table), n, ctypes.byref(x) if x else None, flag, flag_val,
+                                              _ptr(h_done), _stream(stream)), "kvx_handoff_host")

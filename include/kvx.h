@@ -1,0 +1,187 @@
+/*
+ * kvx.h — C ABI of libkvx.so: B200 (sm_100a) prefill→decode paged-KV handoff.
+ *
+ * The reference repository (emolinaro/dynamo-k8s-llm-inference) has no FFI for this path: the
+ * handoff lives inside the `nvcr.io/nvidia/ai-dynamo/{vllm,sglang,tensorrtllm}-runtime:0.8.1` images that its manifests
+ * select (examples/deploy/vllm/disagg.yaml:28,37,57; examples/deploy/sglang/disagg.yaml:45-50,80-85;
+ * examples/deploy/trtllm/disagg.yaml:39-40,62-63).  Each entry point below therefore cites the
+ * manifest line that switches the behaviour on, and the verb of the transfer agent the images use
+ * for it, as seen in the on-box vLLM 0.22 NIXL connector ("[vllm]" =
+ * vllm/distributed/kv_transfer/kv_connector/v1/nixl/, a layout authority, not the reference).
+ *
+ * Conventions
+ *   - every function returns 0 (KVX_OK) or a negative KVX_E* code; nothing throws or exits;
+ *   - the library is asynchronous with respect to the host and ordered on the caller's stream
+ *     (`stream` is a cudaStream_t passed as void*; NULL = the legacy default stream);
+ *   - the caller owns every KV pool, staging buffer and block table; the library owns contexts,
+ *     pool records and its own small scratch;
+ *   - block tables are DEVICE pointers to int32 block ids unless the name says `_host`;
+ *   - a context is used by one host thread at a time; different contexts are independent;
+ *   - there is no CPU fallback: without a CUDA device every compute entry returns KVX_ECUDA.
+ */
+#ifndef KVX_H_
+#define KVX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KVX_ABI_VERSION 0x00010000u
+
+enum {
+  KVX_OK = 0,
+  KVX_EINVAL = -1,       /* bad argument (null, misaligned, out of range)        */
+  KVX_ECUDA = -2,        /* a CUDA call failed; text in kvx_last_error()         */
+  KVX_ENOMEM = -3,       /* host or device allocation failed                     */
+  KVX_EUNSUPPORTED = -4, /* geometry the kernels cannot express                  */
+  KVX_ETIMEOUT = -5,     /* flag did not reach the value in time                 */
+  KVX_ERANGE = -6,       /* caller buffer too small / size beyond a fixed limit  */
+  KVX_EIPC = -7,         /* peer mapping failed                                  */
+  KVX_ENOTREADY = -8     /* kvx_flag_poll: not there yet                         */
+};
+
+enum { KVX_LAYOUT_NHD = 0, KVX_LAYOUT_HND = 1 };
+
+/* Tunables for kvx_ctx_set_option (also read once from the environment as KVX_<NAME>). */
+enum {
+  KVX_OPT_ENGINE = 0,      /* 0 auto, 1 "ldg" (register path), 2 "tma" (bulk-copy pipeline) */
+  KVX_OPT_STAGES = 1,      /* tma: pipeline stages (2..8)                                    */
+  KVX_OPT_STAGE_BYTES = 2, /* tma: bytes per stage (multiple of 1024)                        */
+  KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this                                   */
+  KVX_OPT_STORE_MODE = 4,  /* tma: 0 auto, 1 thread stores, 2 bulk stores                    */
+  KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
+  KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16)                          */
+  KVX_OPT_L2_HINT = 7,     /* 1: evict_first on loads                                        */
+  KVX_OPT__COUNT = 8
+};
+
+typedef struct kvx_ctx kvx_ctx;
+typedef struct kvx_pool kvx_pool;
+
+/*
+ * One worker's paged KV pool = what [vllm] register_kv_caches records (worker.py:788-1012) and
+ * NixlAgentMetadata publishes (metadata.py:41-53): a base address per region (K and V of every
+ * layer are separate regions), the number of blocks, and the byte size of one block of one region.
+ * chunk_bytes = block_tokens * heads * head_dim * elem_bytes.  `block_stride` is the distance in
+ * bytes between block id b and b+1 inside a region: chunk_bytes for split K/V pools
+ * (FlashAttention (2, nb, N, H, D)), 2*chunk_bytes for blocks-first joint pools (FlashInfer
+ * (nb, 2, N, H, D), where V's region base is K's base + chunk_bytes).  0 means chunk_bytes.
+ */
+typedef struct kvx_pool_desc {
+  uint32_t struct_size;  /* sizeof(kvx_pool_desc), for ABI growth */
+  uint32_t regions;      /* number of entries in base[]            */
+  uint32_t block_tokens; /* N (manifests pin 16: sglang/disagg.yaml:39-40) */
+  uint32_t heads;        /* KV heads held by THIS rank             */
+  uint32_t head_dim;     /* D                                      */
+  uint32_t elem_bytes;   /* E (2 = bf16)                           */
+  uint32_t layout;       /* KVX_LAYOUT_NHD: [N][H][D]; KVX_LAYOUT_HND: [H][N][D] */
+  uint32_t tp_rank;
+  uint32_t tp_size;      /* sglang/disagg.yaml:41-42 (--tp)        */
+  uint32_t reserved;
+  uint64_t num_blocks;
+  uint64_t block_stride;
+  void* const* base;     /* host array [regions] of device addresses */
+} kvx_pool_desc;
+
+/*
+ * In-flight transform.  Moves `heads` KV heads starting at local head `src_head_off` of the source
+ * chunk to head slot `dst_head_off` of the destination chunk; heads == 0 means
+ * min(src heads, dst heads) and offsets as given.  This is the TP reshard of [vllm]
+ * tp_mapping.py:65-142 (rank_offset_factor → src_head_off, rank_to_attention_slot → dst_head_off).
+ * `stage_layout` is the row order of the contiguous staging image that kvx_gather writes and
+ * kvx_scatter reads ([regions][n][N*heads*D*E] bytes, heads compacted).  A NULL xform means: all
+ * heads, no offsets, staging in the pool's own layout.
+ */
+typedef struct kvx_xform {
+  uint32_t src_head_off;
+  uint32_t dst_head_off;
+  uint32_t heads;
+  uint32_t stage_layout;
+} kvx_xform;
+
+/* ABI check / messages (static strings; do not free). */
+uint32_t kvx_version(void);
+const char* kvx_strerror(int32_t code);
+/* Text of the last CUDA failure seen by this context ("" if none). */
+const char* kvx_last_error(const kvx_ctx* ctx);
+
+/* Per-worker context: device, scratch, completion flags.  Replaces the NIXL agent a worker
+ * started with --is-prefill-worker / --is-decode-worker creates (vllm/disagg.yaml:37,57). */
+int32_t kvx_ctx_create(int32_t device, kvx_ctx** out);
+int32_t kvx_ctx_destroy(kvx_ctx* ctx);
+int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value);
+int32_t kvx_ctx_get_option(const kvx_ctx* ctx, int32_t option, int64_t* value);
+/* Kernels launched by this context so far (bench.py's gpu_launches). */
+int32_t kvx_ctx_launch_count(const kvx_ctx* ctx, uint64_t* count);
+/* SM count of the context's device. */
+int32_t kvx_ctx_sm_count(const kvx_ctx* ctx, int32_t* sms);
+
+/* Raw device memory that can be exported to a peer process (cudaMalloc, not a caching allocator). */
+int32_t kvx_mem_alloc(kvx_ctx* ctx, uint64_t bytes, void** out);
+int32_t kvx_mem_free(kvx_ctx* ctx, void* ptr);
+/* Serialise / map one device buffer across processes (handshake payload; [vllm]
+ * get_agent_metadata / add_remote_agent, worker.py:991,1309).  *len in: capacity, out: used. */
+int32_t kvx_mem_export(kvx_ctx* ctx, const void* ptr, uint64_t bytes, void* buf, size_t* len);
+int32_t kvx_mem_import(kvx_ctx* ctx, const void* buf, size_t len, void** out);
+int32_t kvx_mem_unmap(kvx_ctx* ctx, void* imported);
+
+/* = register_kv_caches ([vllm] worker.py:788): records addresses, copies nothing. */
+int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** out);
+int32_t kvx_pool_release(kvx_pool* pool);
+int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes);
+/* = agent metadata + add_remote_agent: descriptor + peer handles of every region. */
+int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len);
+int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out);
+
+/* Completion flags: an array of uint64 in this context's device memory that a peer may write
+ * (= NIXL notifications, [vllm] worker.py:2164,1792-1845). */
+int32_t kvx_ctx_flags(kvx_ctx* ctx, uint64_t** flags, uint32_t* count);
+int32_t kvx_flag_reset(kvx_ctx* ctx, uint64_t* flag, uint64_t value, void* stream);
+/* Stream-ordered wait until *flag >= value (bounded: timeout_ms, then the context is marked failed
+ * and the next kvx_flag_poll / kvx_ctx_check returns KVX_ETIMEOUT).  = check_xfer_state polling
+ * ([vllm] worker.py:1868-1913) moved onto the GPU. */
+int32_t kvx_flag_wait(kvx_ctx* ctx, const uint64_t* flag, uint64_t value, uint32_t timeout_ms,
+                      void* stream);
+/* Host-side check: KVX_OK if *flag >= value, else KVX_ENOTREADY. Synchronous 8-byte read. */
+int32_t kvx_flag_poll(kvx_ctx* ctx, const uint64_t* flag, uint64_t value);
+/* KVX_OK unless a stream-ordered wait timed out since the last call. */
+int32_t kvx_ctx_check(kvx_ctx* ctx);
+
+/* H1+H2(+H3 source slice): gather the request's n blocks of every region from the paged pool into
+ * the contiguous staging image, transforming the layout on the way.  Replaces the descriptor list
+ * of [vllm] worker.py:2202-2213 and the receive-side permute of kv_connector/utils.py:255-277. */
+int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, uint32_t n,
+                   void* staging, const kvx_xform* xf, void* stream);
+
+/* H4+H6: contiguous copy into (peer) memory, then release-store flag_val to *flag (flag may be
+ * NULL).  = make_prepped_xfer("READ") + transfer + notif ([vllm] worker.py:2220-2233). */
+int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint64_t* flag,
+                 uint64_t flag_val, void* stream);
+
+/* H5(+H3 destination slot): scatter a staging image into the pool's freshly allocated blocks. */
+int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, const int32_t* d_table,
+                    uint32_t n, const kvx_xform* xf, void* stream);
+
+/* H1-H6 in one kernel: source blocks → shared memory → destination blocks (local or peer pool),
+ * then the completion flag.  `flag` may be NULL. */
+int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table,
+                          const kvx_pool* dst, const int32_t* d_dst_table, uint32_t n,
+                          const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);
+
+/* The call a serving engine makes per request ([vllm] kv_transfer_params, scheduler.py:664-674):
+ * block-id lists arrive in HOST memory.  Uploads both tables into context scratch, runs the fused
+ * handoff, and — when `h_done` is not NULL — copies the completion flag back into *h_done (pinned
+ * or pageable host memory) on the same stream.  n is bounded by KVX_MAX_HOST_TABLE. */
+#define KVX_MAX_HOST_TABLE (1u << 20)
+int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table,
+                         const kvx_pool* dst, const int32_t* h_dst_table, uint32_t n,
+                         const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, uint64_t* h_done,
+                         void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KVX_H_ */

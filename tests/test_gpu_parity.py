@@ -1,0 +1,259 @@
+"""Parity tests proper: libkvx.so (through the C ABI) against the oracle, bit for bit."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import kvx
+from gpu_util import ENGINE_CONFIGS, DevPool, cfg_id, dev_table, xf_c
+from oracle import kvx_oracle as o
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = kvx.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.fixture(params=ENGINE_CONFIGS, ids=cfg_id)
+def cfg_ctx(request):
+    c = kvx.Context(0, **request.param)
+    yield c
+    c.check()
+    c.close()
+
+
+SHAPES = [
+    # L, H, D, src layout, dst layout, src arrangement, dst arrangement, n
+    (2, 8, 64, o.NHD, o.NHD, "split", "split", 37),       # Llama-3.2-1B chunk, identity
+    (2, 8, 128, o.HND, o.NHD, "split", "split", 70),      # vLLM P (HND) → NHD decode
+    (2, 8, 128, o.NHD, o.HND, "split", "blocks_first", 33),
+    (1, 8, 128, o.HND, o.HND, "blocks_first", "split", 5),
+    (3, 2, 128, o.HND, o.NHD, "split", "split", 1),        # TP4 shard chunk (8 KiB)
+    (1, 4, 32, o.NHD, o.HND, "split", "split", 300),       # many small chunks, > one table batch
+]
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: f"L{s[0]}H{s[1]}D{s[2]}-{s[3]}{s[4]}-{s[5][0]}{s[6][0]}-n{s[7]}")
+def test_fused_handoff_matches_oracle(cfg_ctx, shape):
+    L, H, D, ls, ld, as_, ad, n = shape
+    nbp, nbd = n + 9, n + 14
+    src = o.make_pool(L, H, D, nbp, ls, arrangement=as_, seed=11)
+    dst = o.make_pool(L, H, D, nbd, ld, arrangement=ad, fill="canary")
+    ts, td = o.make_table(nbp, n, 3), o.make_table(nbd, n, 4)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n)
+    torch.cuda.synchronize()
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(ddst.bytes(), dst.buf)          # touched == expected, untouched == canary
+    assert np.array_equal(dsrc.bytes(), src.buf)          # source unchanged
+
+
+@pytest.mark.parametrize("stage_layout", [o.NHD, o.HND])
+@pytest.mark.parametrize("shape", SHAPES[:4], ids=lambda s: f"L{s[0]}H{s[1]}D{s[2]}-{s[3]}{s[4]}")
+def test_gather_copy_scatter_matches_oracle(cfg_ctx, shape, stage_layout):
+    L, H, D, ls, ld, as_, ad, n = shape
+    nbp, nbd = n + 5, n + 6
+    src = o.make_pool(L, H, D, nbp, ls, arrangement=as_, seed=21)
+    dst = o.make_pool(L, H, D, nbd, ld, arrangement=ad, fill="canary")
+    ts, td = o.make_table(nbp, n, 8), o.make_table(nbd, n, 9)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    img_bytes = src.regions * n * src.chunk_bytes
+    stage_p = torch.full((img_bytes,), 0xAB, dtype=torch.uint8, device="cuda")
+    stage_d = torch.full((img_bytes + 64,), 0xCD, dtype=torch.uint8, device="cuda")
+    xf = kvx.Xform(0, 0, 0, stage_layout)
+    cfg_ctx.gather(dsrc.kp, dev_table(ts), n, stage_p, xf)
+    flags, _ = cfg_ctx.flags()
+    cfg_ctx.flag_reset(flags + 8 * 5, 0)
+    cfg_ctx.copy(stage_p, stage_d, img_bytes, flag=flags + 8 * 5, flag_val=42)
+    cfg_ctx.scatter(stage_d, ddst.kp, dev_table(td), n, xf)
+    torch.cuda.synchronize()
+    want_img = o.gather(src, ts, o.Xform(stage_layout=stage_layout))
+    assert np.array_equal(stage_p.cpu().numpy(), want_img.reshape(-1))
+    got_d = stage_d.cpu().numpy()
+    assert np.array_equal(got_d[:img_bytes], want_img.reshape(-1))
+    assert (got_d[img_bytes:] == 0xCD).all()              # copy wrote exactly `bytes`
+    assert cfg_ctx.flag_poll(flags + 8 * 5, 42)
+    o.scatter(want_img, dst, td, o.Xform(stage_layout=stage_layout))
+    assert np.array_equal(ddst.bytes(), dst.buf)
+
+
+@pytest.mark.parametrize("layouts", [(o.HND, o.HND), (o.HND, o.NHD), (o.NHD, o.NHD), (o.NHD, o.HND)],
+                         ids=["HH", "HN", "NN", "NH"])
+@pytest.mark.parametrize("tp", [(4, 2), (2, 4), (1, 2), (4, 1)], ids=lambda t: f"P{t[0]}D{t[1]}")
+def test_tp_reshard_edges(cfg_ctx, tp, layouts):
+    """Config #4 in small: every P rank → D rank edge with its head slice, fan-in into one D pool."""
+    p_tp, d_tp = tp
+    lp, ld = layouts
+    L, Ht, D, n = 2, 8, 128, 19
+    hp, hd = Ht // p_tp, Ht // d_tp
+    ts = o.make_table(n + 3, n, 31)
+    p_pools = [o.make_pool(L, hp, D, n + 3, lp, seed=100 + r, tp_rank=r, tp_size=p_tp) for r in range(p_tp)]
+    dev_p = [DevPool(cfg_ctx, p) for p in p_pools]
+    for j in range(d_tp):
+        dpool = o.make_pool(L, hd, D, n + 7, ld, fill="canary", tp_rank=j, tp_size=d_tp)
+        ddev = DevPool(cfg_ctx, dpool)
+        td = o.make_table(n + 7, n, 200 + j)
+        for e in o.tp_mapping(d_tp, p_tp, j, Ht).edges:
+            o.handoff(p_pools[e.p_rank], ts, dpool, td, e.xform)
+            cfg_ctx.handoff_fused(dev_p[e.p_rank].kp, dev_table(ts), ddev.kp, dev_table(td), n, xf_c(e.xform, ld))
+        torch.cuda.synchronize()
+        assert np.array_equal(ddev.bytes(), dpool.buf)
+
+
+def test_tp_reshard_staged(ctx):
+    """gather(head slice) → copy → scatter(head slot) for TP4→TP2 equals the oracle."""
+    L, D, n = 2, 128, 11
+    p_pools = [o.make_pool(L, 2, D, n + 2, o.HND, seed=5 + r) for r in range(2)]
+    dpool = o.make_pool(L, 4, D, n + 4, o.NHD, fill="canary")
+    ddev = DevPool(ctx, dpool)
+    ts, td = o.make_table(n + 2, n, 1), o.make_table(n + 4, n, 2)
+    for r, pp in enumerate(p_pools):
+        xf = o.Xform(0, 2 * r, 2, o.NHD)
+        dp = DevPool(ctx, pp)
+        img = torch.empty(pp.regions * n * pp.chunk_bytes, dtype=torch.uint8, device="cuda")
+        ctx.gather(dp.kp, dev_table(ts), n, img, xf_c(xf, o.NHD))
+        ctx.scatter(img, ddev.kp, dev_table(td), n, xf_c(xf, o.NHD))
+        torch.cuda.synchronize()
+        want = o.gather(pp, ts, xf)
+        assert np.array_equal(img.cpu().numpy(), want.reshape(-1))
+        o.scatter(want, dpool, td, xf)
+    assert np.array_equal(ddev.bytes(), dpool.buf)
+
+
+def test_golden_fixture_on_gpu(cfg_ctx, golden_dir):
+    g = np.load(os.path.join(golden_dir, "layout_hnd_to_nhd.npz"))
+    L, H, N, D, nb_p, nb_d, n = [int(x) for x in g["shape"]]
+    from test_oracle import _pool_from_regions
+
+    src = _pool_from_regions(g["p_pool"], o.HND, H, D, N)
+    dst = _pool_from_regions(np.full((2 * L, nb_d, N, H, D), o.CANARY16, dtype=np.uint16), o.NHD, H, D, N)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(g["p_table"]), ddst.kp, dev_table(g["d_table"]), n)
+    torch.cuda.synchronize()
+    assert np.array_equal(ddst.bytes(), np.ascontiguousarray(g["d_expect"]).view(np.uint8).reshape(-1))
+
+
+def test_empty_and_single(ctx):
+    src = o.make_pool(1, 8, 64, 4, o.NHD, seed=1)
+    dst = o.make_pool(1, 8, 64, 4, o.HND, fill="canary")
+    dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
+    flags, _ = ctx.flags()
+    ctx.flag_reset(flags, 0)
+    ctx.handoff_fused(dsrc.kp, None, ddst.kp, None, 0, flag=flags, flag_val=7)  # full prefix hit: notify only
+    torch.cuda.synchronize()
+    assert ctx.flag_poll(flags, 7)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    ctx.handoff_fused(dsrc.kp, dev_table([3]), ddst.kp, dev_table([1]), 1, flag=flags, flag_val=8)
+    torch.cuda.synchronize()
+    assert ctx.flag_poll(flags, 8) and not ctx.flag_poll(flags, 9)
+    o.handoff(src, [3], dst, [1])
+    assert np.array_equal(ddst.bytes(), dst.buf)
+
+
+def test_host_table_entry(ctx):
+    """kvx_handoff_host: block ids arrive in host memory; completion comes back to the host."""
+    src = o.make_pool(2, 8, 128, 70, o.HND, seed=4)
+    dst = o.make_pool(2, 8, 128, 80, o.NHD, fill="canary")
+    ts, td = o.make_table(70, 64, 5), o.make_table(80, 64, 6)
+    dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
+    done = torch.zeros(1, dtype=torch.int64).pin_memory()
+    ctx.handoff_host(dsrc.kp, ts, ddst.kp, td, 64, flag_val=99, h_done=done)
+    torch.cuda.synchronize()
+    assert int(done[0]) == 99
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    bad = td.copy()
+    bad[3] = 80
+    with pytest.raises(kvx.KvxError) as e:
+        ctx.handoff_host(dsrc.kp, ts, ddst.kp, bad, 64)
+    assert e.value.code == kvx.api.ERANGE
+
+
+@pytest.mark.parametrize("engine", ["ldg", "tma"])
+def test_bad_device_table_is_skipped_and_reported(engine):
+    c = kvx.Context(0, engine=engine)
+    src = o.make_pool(1, 8, 64, 6, o.NHD, seed=1)
+    dst = o.make_pool(1, 8, 64, 6, o.NHD, fill="canary")
+    dsrc, ddst = DevPool(c, src), DevPool(c, dst)
+    c.handoff_fused(dsrc.kp, dev_table([1, 2, 3]), ddst.kp, dev_table([1, 6, 3]), 3)  # id 6 is out of range
+    torch.cuda.synchronize()
+    with pytest.raises(kvx.KvxError) as e:
+        c.check()
+    assert e.value.code == kvx.api.ERANGE
+    o.handoff(src, [1, 3], dst, [1, 3])  # the bad item moved nothing
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    c.check()
+    c.close()
+
+
+@pytest.mark.parametrize("nbytes", [16, 4096 + 16, 32768, 3 * 32768 + 48, (1 << 20) + 32, 9 << 20])
+def test_copy_sizes(cfg_ctx, nbytes):
+    a = torch.randint(0, 256, (nbytes + 32,), dtype=torch.uint8, device="cuda")
+    b = torch.full((nbytes + 32,), 0x5A, dtype=torch.uint8, device="cuda")
+    cfg_ctx.copy(a[16:], b[16:], nbytes)
+    torch.cuda.synchronize()
+    assert torch.equal(a[16 : 16 + nbytes], b[16 : 16 + nbytes])
+    assert (b[:16] == 0x5A).all() and (b[16 + nbytes :] == 0x5A).all()
+
+
+def test_argument_errors(ctx):
+    src = o.make_pool(1, 8, 64, 4, o.NHD, seed=1)
+    dsrc = DevPool(ctx, src)
+    with pytest.raises(kvx.KvxError):  # misaligned staging
+        ctx.gather(dsrc.kp, dev_table([1]), 1, dsrc.t.data_ptr() + 8)
+    with pytest.raises(kvx.KvxError):  # head slice out of range
+        ctx.gather(dsrc.kp, dev_table([1]), 1, dsrc.t, kvx.Xform(6, 0, 4, 0))
+    with pytest.raises(kvx.KvxError):  # copy size not a multiple of 16
+        ctx.copy(dsrc.t, dsrc.t, 24)
+    other = o.make_pool(1, 8, 128, 4, o.NHD, seed=1)
+    with pytest.raises(kvx.KvxError):  # shapes differ
+        ctx.handoff_fused(dsrc.kp, dev_table([1]), DevPool(ctx, other).kp, dev_table([1]), 1)
+
+
+@pytest.mark.parametrize("cfg", [dict(engine="tma"), dict(engine="ldg")], ids=cfg_id)
+def test_full_size_properties_qwen3_32k(cfg):
+    """BASELINE config #2 at its largest size (Qwen3-0.6B KV shape, ISL 32k, 3.5 GiB payload), checked
+    by size-independent properties on the device: HND→NHD→HND round trip restores the request's
+    blocks bit for bit, a word checksum is preserved by each hop, untouched blocks keep the canary."""
+    from kvx import synth
+
+    c = kvx.Context(0, **cfg)
+    shape = kvx.KV_SHAPES["Qwen/Qwen3-0.6B"]
+    n = shape.blocks_for(32768)
+    nb = n + 129
+    P = synth.alloc_pool(c, shape, nb, kvx.HND)
+    Dp = synth.alloc_pool(c, shape, nb, kvx.NHD)
+    P2 = synth.alloc_pool(c, shape, nb, kvx.HND)
+    synth.fill_random(P, 1234)
+    synth.fill_canary(Dp)
+    synth.fill_canary(P2)
+    t1, t2, t3 = synth.make_table(nb, n, 1), synth.make_table(nb, n, 2), synth.make_table(nb, n, 3)
+    c.handoff_fused(P.pool, dev_table(t1), Dp.pool, dev_table(t2), n)
+    c.handoff_fused(Dp.pool, dev_table(t2), P2.pool, dev_table(t3), n)
+    torch.cuda.synchronize()
+    c.check()
+    chunk_words = shape.chunk_bytes() // 2
+
+    def view(dp):
+        return dp.tensor().view(torch.int16).view(shape.regions, nb, chunk_words)
+
+    i1, i2, i3 = (torch.from_numpy(t.astype(np.int64)).cuda() for t in (t1, t2, t3))
+    a, m, b = view(P)[:, i1], view(Dp)[:, i2], view(P2)[:, i3]
+    assert torch.equal(a, b)
+    # per-chunk checksum survives the permutation
+    assert torch.equal(a.to(torch.int64).sum(-1), m.to(torch.int64).sum(-1))
+    # the middle hop really is the NHD image of the HND source
+    N, H, Dh = shape.block_tokens, shape.kv_heads, shape.head_dim
+    assert torch.equal(a.view(shape.regions, n, H, N, Dh).transpose(2, 3), m.view(shape.regions, n, N, H, Dh))
+    canary = np.array(synth.CANARY16, dtype=np.uint16).view(np.int16).item()
+    mask = torch.ones(nb, dtype=torch.bool, device="cuda")
+    mask[i2] = False
+    assert (view(Dp)[:, mask] == canary).all()
+    for dp in (P, Dp, P2):
+        dp.free()
+    c.close()

@@ -1,0 +1,182 @@
+"""CPU tests of the oracle itself: golden vectors, numpy vs C restatement, domain properties."""
+import json
+import os
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from oracle import kvx_oracle as o
+from oracle import kvx_oracle_c as oc
+
+pytestmark = pytest.mark.filterwarnings("ignore")
+
+
+def _pool_from_regions(arr: np.ndarray, layout: int, heads: int, head_dim: int, N: int = 16, E: int = 2) -> o.Pool:
+    """arr: [regions, num_blocks, ...chunk...] uint16 → split-arrangement Pool over its bytes."""
+    regions, nb = arr.shape[0], arr.shape[1]
+    buf = np.ascontiguousarray(arr).view(np.uint8).reshape(-1).copy()
+    chunk = buf.size // (regions * nb)
+    return o.Pool(buf, [r * nb * chunk for r in range(regions)], nb, chunk, N, heads, head_dim, E, layout)
+
+
+def test_golden_layout_hnd_to_nhd(golden_dir):
+    """Oracle handoff HND→NHD == raw landing + vLLM kv_postprocess_layout_on_receive."""
+    g = np.load(os.path.join(golden_dir, "layout_hnd_to_nhd.npz"))
+    L, H, N, D, nb_p, nb_d, n = [int(x) for x in g["shape"]]
+    src = _pool_from_regions(g["p_pool"], o.HND, H, D, N)
+    dst = _pool_from_regions(np.full((2 * L, nb_d, N, H, D), o.CANARY16, dtype=np.uint16), o.NHD, H, D, N)
+    o.handoff(src, g["p_table"], dst, g["d_table"])
+    want = np.ascontiguousarray(g["d_expect"]).view(np.uint8).reshape(-1)
+    assert np.array_equal(dst.buf, want)
+    # and the C restatement
+    dst2 = _pool_from_regions(np.full((2 * L, nb_d, N, H, D), o.CANARY16, dtype=np.uint16), o.NHD, H, D, N)
+    assert oc.handoff(src, g["p_table"], dst2, g["d_table"], threads=3) == 0
+    assert np.array_equal(dst2.buf, want)
+
+
+def test_golden_tp_mapping(golden_dir):
+    rows = json.load(open(os.path.join(golden_dir, "tp_mapping.json")))["rows"]
+    assert len(rows) >= 30
+    for row in rows:
+        m = o.tp_mapping(row["d_tp"], row["p_tp"], row["d_rank"], row["total_kv_heads"])
+        assert list(m.source_ranks) == row["source_ranks"], row
+        assert {str(k): v for k, v in m.rank_to_slot.items()} == row["rank_to_slot"], row
+        assert m.rank_offset_factor == row["rank_offset_factor"], row
+
+
+def test_survey_known_answers():
+    """SURVEY.md §8c table."""
+    m = o.tp_mapping(2, 4, 1, 8)
+    assert m.tp_ratio == -2 and m.source_ranks == (2, 3) and m.rank_to_slot == {2: 0, 3: 1}
+    m = o.tp_mapping(4, 2, 3, 8)
+    assert m.tp_ratio == 2 and m.source_ranks == (1,) and m.rank_offset_factor == 1
+    m = o.tp_mapping(1, 4, 0, 8)
+    assert m.tp_ratio == -4 and m.rank_to_slot == {0: 0, 1: 1, 2: 2, 3: 3}
+
+
+CASES = [
+    # (layers, heads, head_dim, src_layout, dst_layout, arrangement_src, arrangement_dst)
+    (2, 8, 64, o.HND, o.NHD, "split", "split"),
+    (2, 8, 64, o.NHD, o.HND, "split", "blocks_first"),
+    (1, 4, 128, o.NHD, o.NHD, "blocks_first", "split"),
+    (3, 2, 32, o.HND, o.HND, "split", "split"),
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_numpy_vs_c_and_canary(case):
+    L, H, D, ls, ld, as_, ad = case
+    src = o.make_pool(L, H, D, 23, ls, arrangement=as_, seed=1)
+    dst = o.make_pool(L, H, D, 29, ld, arrangement=ad, fill="canary")
+    dst_c = o.make_pool(L, H, D, 29, ld, arrangement=ad, fill="canary")
+    ts, td = o.make_table(23, 9, 5), o.make_table(29, 9, 6)
+    o.handoff(src, ts, dst, td)
+    assert oc.handoff(src, ts, dst_c, td, threads=4) == 0
+    assert np.array_equal(dst.buf, dst_c.buf)
+    # untouched blocks keep the canary; touched blocks hold the source rows
+    canary = o.make_pool(L, H, D, 29, ld, arrangement=ad, fill="canary")
+    touched = np.zeros(29, bool)
+    touched[td] = True
+    for r in range(dst.regions):
+        v, c = dst.region_view(r), canary.region_view(r)
+        assert np.array_equal(v[~touched], c[~touched])
+        a = o._rows(src.region_view(r)[ts], ls, 16, H, D * 2)
+        b = o._rows(v[td], ld, 16, H, D * 2)
+        assert np.array_equal(a, b)
+
+
+def test_gather_scatter_compose_equals_handoff():
+    src = o.make_pool(2, 8, 64, 17, o.HND, seed=3)
+    d1 = o.make_pool(2, 8, 64, 19, o.NHD, fill="canary")
+    d2 = o.make_pool(2, 8, 64, 19, o.NHD, fill="canary")
+    ts, td = o.make_table(17, 7, 1), o.make_table(19, 7, 2)
+    for stage_layout in (o.NHD, o.HND):
+        img = o.gather(src, ts, o.Xform(stage_layout=stage_layout))
+        img_c = oc.gather(src, ts, o.Xform(stage_layout=stage_layout), threads=2)
+        assert np.array_equal(img, img_c)
+        o.scatter(o.copy(img), d1, td, o.Xform(stage_layout=stage_layout))
+    o.handoff(src, ts, d2, td)
+    assert np.array_equal(d1.buf, d2.buf)
+
+
+def test_round_trip_is_identity():
+    """encode → decode: P(HND) → D(NHD) → P'(HND) restores the request's blocks bit for bit."""
+    src = o.make_pool(2, 8, 128, 13, o.HND, seed=9)
+    mid = o.make_pool(2, 8, 128, 13, o.NHD, fill="canary")
+    back = o.make_pool(2, 8, 128, 13, o.HND, fill="canary")
+    t = o.make_table(13, 12, 4)
+    o.handoff(src, t, mid, t)
+    o.handoff(mid, t, back, t)
+    for r in range(src.regions):
+        assert np.array_equal(src.region_view(r)[t], back.region_view(r)[t])
+
+
+def test_prefix_hits():
+    src = o.make_pool(1, 2, 32, 9, o.NHD, seed=2)
+    dst = o.make_pool(1, 2, 32, 9, o.NHD, fill="canary")
+    before = dst.buf.copy()
+    o.handoff(src, [1, 2, 3], dst, [])  # full prefix hit: nothing moves
+    assert np.array_equal(dst.buf, before)
+    o.handoff(src, [1, 2, 3, 4], dst, [7, 8])  # partial: last two source blocks
+    for r in range(2):
+        assert np.array_equal(dst.region_view(r)[[7, 8]], src.region_view(r)[[3, 4]])
+
+
+def test_bad_block_ids_raise():
+    src = o.make_pool(1, 2, 32, 5, o.NHD, seed=2)
+    with pytest.raises(IndexError):
+        o.gather(src, [1, 5])
+    with pytest.raises(IndexError):
+        o.gather(src, [-1])
+
+
+@pytest.mark.parametrize("p_tp,d_tp", [(4, 2), (2, 4), (4, 1), (1, 2), (2, 2)])
+@pytest.mark.parametrize("layouts", [(o.HND, o.HND), (o.HND, o.NHD), (o.NHD, o.NHD), (o.NHD, o.HND)])
+def test_tp_reshard_against_global_truth(p_tp, d_tp, layouts):
+    """Build a global KV [regions, blocks, N, H_total, R]; shard heads over P ranks; after all edges
+    every D rank's blocks equal its own head shard of the global truth (SURVEY.md §8c identity)."""
+    lp, ld = layouts
+    L, Ht, D, N, nb, n = 2, 8, 32, 16, 11, 6
+    R = D * 2
+    rng = np.random.Generator(np.random.PCG64(77))
+    truth = rng.integers(0, 256, size=(2 * L, nb, N, Ht, R), dtype=np.uint8)
+    hp, hd = Ht // p_tp, Ht // d_tp
+    t_src = o.make_table(nb, n, 1)
+    p_pools = []
+    for r in range(p_tp):
+        pool = o.make_pool(L, hp, D, nb, lp, fill="canary", tp_rank=r, tp_size=p_tp)
+        for reg in range(2 * L):
+            pool.region_view(reg)[:] = o._pack(truth[reg][:, :, r * hp : (r + 1) * hp, :], lp)
+        p_pools.append(pool)
+    for j in range(d_tp):
+        dpool = o.make_pool(L, hd, D, nb + 2, ld, fill="canary", tp_rank=j, tp_size=d_tp)
+        dpool_c = o.make_pool(L, hd, D, nb + 2, ld, fill="canary", tp_rank=j, tp_size=d_tp)
+        t_dst = o.make_table(nb + 2, n, 100 + j)
+        m = o.tp_mapping(d_tp, p_tp, j, Ht)
+        for e in m.edges:
+            o.handoff(p_pools[e.p_rank], t_src, dpool, t_dst, e.xform)
+            assert oc.handoff(p_pools[e.p_rank], t_src, dpool_c, t_dst, e.xform, threads=2) == 0
+        for reg in range(2 * L):
+            got = o._rows(dpool.region_view(reg)[t_dst], ld, N, hd, R)
+            assert np.array_equal(got, truth[reg][t_src][:, :, j * hd : (j + 1) * hd, :])
+        assert np.array_equal(dpool.buf, dpool_c.buf)
+
+
+@settings(max_examples=40, deadline=None)
+@given(
+    L=st.integers(1, 3), H=st.sampled_from([1, 2, 4, 8]), D=st.sampled_from([8, 16, 64]),
+    N=st.sampled_from([1, 4, 16]), n=st.integers(0, 7), ls=st.sampled_from([0, 1]), ld=st.sampled_from([0, 1]),
+    so=st.integers(0, 3), do=st.integers(0, 3), hc=st.integers(1, 4), seed=st.integers(0, 2**16),
+)
+def test_property_numpy_equals_c(L, H, D, N, n, ls, ld, so, do, hc, seed):
+    Hs, Hd = H + so, H + do  # source / destination chunks with room for the offsets
+    hc = min(hc, H)
+    src = o.make_pool(L, Hs, D, 9, ls, block_tokens=N, seed=seed)
+    d1 = o.make_pool(L, Hd, D, 10, ld, block_tokens=N, fill="canary")
+    d2 = o.make_pool(L, Hd, D, 10, ld, block_tokens=N, fill="canary")
+    ts, td = o.make_table(9, n, seed), o.make_table(10, n, seed + 1)
+    xf = o.Xform(so, do, hc)
+    o.handoff(src, ts, d1, td, xf)
+    assert oc.handoff(src, ts, d2, td, xf, threads=2) == 0
+    assert np.array_equal(d1.buf, d2.buf)
