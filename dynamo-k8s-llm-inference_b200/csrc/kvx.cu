@@ -288,7 +288,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (ok32 && src_bases) for (void* b : *src_bases) ok32 = ok32 && (reinterpret_cast<uintptr_t>(b) % 32 == 0);
   if (ok32 && dst_bases) for (void* b : *dst_bases) ok32 = ok32 && (reinterpret_cast<uintptr_t>(b) % 32 == 0);
   if (p.tail_bytes % 32 != 0) ok32 = false;
-  if (vec_opt == 0) vec_opt = ok32 ? 32 : 16;
+  if (vec_opt == 0) vec_opt = 16;  // measured: 16-byte stores beat 32-byte ones on B200 for this path
   if (vec_opt == 32 && !ok32) vec_opt = 16;
 
   const uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
@@ -297,7 +297,9 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (engine == kEngineTma) {
     const bool dst_single_run = pl.d_runs == 1;
     int mode = store_mode;  // 1 thread stores, 2 bulk stores
-    if (mode == 0) mode = dst_single_run ? 2 : 1;
+    // measured (profiles/r01_sweep.md): thread stores match or beat bulk stores at the default stage size
+    if (mode == 0) mode = 1;
+    (void)dst_single_run;
     const size_t smem = static_cast<size_t>(stages) * stage_bytes;
     if (mode == 2) {
       if (stages < 2) return KVX_EINVAL;
@@ -520,11 +522,11 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   if (cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking) != cudaSuccess) return fail(KVX_ECUDA);
   ctx->opt[KVX_OPT_ENGINE] = env_or("KVX_ENGINE", 0);
   ctx->opt[KVX_OPT_STAGES] = env_or("KVX_STAGES", 4);
-  ctx->opt[KVX_OPT_STAGE_BYTES] = env_or("KVX_STAGE_BYTES", 32768);
-  ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 1);
+  ctx->opt[KVX_OPT_STAGE_BYTES] = env_or("KVX_STAGE_BYTES", 16384);
+  ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 2);
   ctx->opt[KVX_OPT_STORE_MODE] = env_or("KVX_STORE_MODE", 0);
   ctx->opt[KVX_OPT_VEC_BYTES] = env_or("KVX_VEC_BYTES", 0);
-  ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 8);
+  ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
   *out = ctx;
   return KVX_OK;

@@ -87,9 +87,16 @@ __device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, uint32_t 
   return ok != 0;
 }
 // Bounded wait: a pipeline bug must trap, not hang the GPU.
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
-  for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins) {
-    if (spins > (1u << 26)) __trap();
+  if (mbar_try_wait(bar, parity)) return;
+  const unsigned long long t0 = global_timer_ns();
+  for (uint32_t spins = 1; !mbar_try_wait(bar, parity); ++spins) {
+    if ((spins & 0xffu) == 0 && global_timer_ns() - t0 > 4000000000ull) __trap();  // 4 s: never a hang
   }
 }
 __device__ __forceinline__ unsigned long long l2_policy_evict_first() {
