@@ -911,3 +911,164 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// kvx_handoff_static: the fused handoff with all scratch in one fixed device array (see kvx.h).
+// =================================================================================================
+namespace {
+
+// Layout of the array, in bytes: [src region bases][dst region bases][src table][dst table][counter, status].
+constexpr size_t kStaticBasesBytes = static_cast<size_t>(KVX_STATIC_MAX_REGIONS) * sizeof(unsigned long long);
+constexpr size_t kStaticTableBytes = static_cast<size_t>(KVX_STATIC_MAX_BLOCKS) * sizeof(int);
+constexpr size_t kStaticOffSrcBases = 0;
+constexpr size_t kStaticOffDstBases = kStaticBasesBytes;
+constexpr size_t kStaticOffSrcTable = 2 * kStaticBasesBytes;
+constexpr size_t kStaticOffDstTable = kStaticOffSrcTable + kStaticTableBytes;
+constexpr size_t kStaticOffWords = kStaticOffDstTable + kStaticTableBytes;  // counter at +0, status at +4
+static_assert(kStaticOffWords + 256 == KVX_STATIC_SCRATCH_BYTES, "scratch layout and header limit disagree");
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never a device address.
+static __device__ __align__(256) unsigned char g_static_scratch[KVX_STATIC_SCRATCH_BYTES];
+
+constexpr int kStaticMaxDevices = 64;
+constexpr uint32_t kStaticStages = 4, kStaticStageBytes = 16384, kStaticConsumerWarps = 16, kStaticCtasPerSm = 2;
+
+struct StaticDevice {
+  bool ready = false;
+  unsigned char* scratch = nullptr;  // device address of g_static_scratch on this device
+  int sms = 0;
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mu;
+
+// Once per device, with that device current: resolve the array's device address, size the kernel's
+// shared memory, read the SM count.  None of these calls allocates.
+int32_t static_setup(int device, StaticDevice** out) {
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  StaticDevice& d = g_static_dev[device];
+  if (!d.ready) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      (void)cudaGetLastError();
+      return KVX_ECUDA;
+    }
+    e = cudaFuncSetAttribute(kvx::kvx_xfer_tma_kernel<16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             static_cast<int>(kStaticStages * kStaticStageBytes));
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return KVX_ECUDA;
+    }
+    d.scratch = static_cast<unsigned char*>(ptr);
+    d.ready = true;
+  }
+  *out = &d;
+  return KVX_OK;
+}
+
+int32_t static_check_desc(const kvx_pool_desc* d, uint64_t* chunk, uint64_t* stride) {
+  if (!d || !d->base || d->struct_size != sizeof(kvx_pool_desc)) return KVX_EINVAL;
+  if (d->regions == 0 || d->block_tokens == 0 || d->heads == 0 || d->head_dim == 0 || d->elem_bytes == 0 ||
+      d->num_blocks == 0)
+    return KVX_EINVAL;
+  if (d->layout != KVX_LAYOUT_NHD && d->layout != KVX_LAYOUT_HND) return KVX_EINVAL;
+  if (d->regions > KVX_STATIC_MAX_REGIONS) return KVX_ERANGE;
+  const uint64_t row = static_cast<uint64_t>(d->head_dim) * d->elem_bytes;
+  if (row % 16 != 0) return KVX_EUNSUPPORTED;
+  *chunk = row * d->heads * d->block_tokens;
+  if (*chunk >= (1ull << 31)) return KVX_EUNSUPPORTED;
+  *stride = d->block_stride ? d->block_stride : *chunk;
+  if (*stride < *chunk || *stride % 16 != 0) return KVX_EINVAL;
+  for (uint32_t r = 0; r < d->regions; ++r)
+    if (!d->base[r] || reinterpret_cast<uintptr_t>(d->base[r]) % 16 != 0) return KVX_EINVAL;
+  return KVX_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, const int32_t* h_src_table,
+                                      const kvx_pool_desc* dst, const int32_t* h_dst_table, uint32_t n,
+                                      const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream) {
+  if (device < 0 || device >= kStaticMaxDevices) return KVX_EINVAL;
+  if (n > KVX_STATIC_MAX_BLOCKS) return KVX_ERANGE;  // beyond the fixed table capacity
+  uint64_t s_chunk = 0, s_stride = 0, d_chunk = 0, d_stride = 0;
+  int32_t rc = static_check_desc(src, &s_chunk, &s_stride);
+  if (rc) return rc;
+  rc = static_check_desc(dst, &d_chunk, &d_stride);
+  if (rc) return rc;
+  if (!same_shape(*src, *dst)) return KVX_EINVAL;
+  if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
+  for (uint32_t i = 0; i < n; ++i) {
+    if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->num_blocks) return KVX_ERANGE;
+    if (h_dst_table[i] < 0 || static_cast<uint64_t>(h_dst_table[i]) >= dst->num_blocks) return KVX_ERANGE;
+  }
+  uint32_t so, dof, hc, sl;
+  rc = resolve_xform(src, dst, xf, &so, &dof, &hc, &sl, src->layout);
+  if (rc) return rc;
+
+  DeviceGuard guard(device);
+  if (!guard.ok) {
+    (void)cudaGetLastError();
+    return KVX_ECUDA;
+  }
+  StaticDevice* dev = nullptr;
+  rc = static_setup(device, &dev);  // first call on this device: do it before any stream capture
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  auto bad = [](cudaError_t e) {
+    if (e == cudaSuccess) return false;
+    (void)cudaGetLastError();
+    return true;
+  };
+  if (n == 0) {  // nothing to move: notify only
+    if (flag && bad(cudaMemcpyAsync(flag, &flag_val, sizeof(flag_val), cudaMemcpyHostToDevice, st))) return KVX_ECUDA;
+    return KVX_OK;
+  }
+
+  Plan pl{};
+  rc = make_plan(src->block_tokens, src->head_dim * src->elem_bytes, hc, ChunkGeom{src->layout, src->heads, so},
+                 ChunkGeom{dst->layout, dst->heads, dof}, kStaticStageBytes, &pl);
+  if (rc) return rc;  // a head/token unit larger than one 16 KiB stage is not supported here
+  const uint64_t total = static_cast<uint64_t>(n) * src->regions * pl.ppc;
+  if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;
+
+  unsigned char* sc = dev->scratch;
+  // The array keeps whatever the previous call left: upload everything this launch reads and zero
+  // the counter and status word, all ordered on the caller's stream.
+  if (bad(cudaMemcpyAsync(sc + kStaticOffSrcBases, src->base, src->regions * sizeof(void*), cudaMemcpyHostToDevice, st)) ||
+      bad(cudaMemcpyAsync(sc + kStaticOffDstBases, dst->base, dst->regions * sizeof(void*), cudaMemcpyHostToDevice, st)) ||
+      bad(cudaMemcpyAsync(sc + kStaticOffSrcTable, h_src_table, n * sizeof(int), cudaMemcpyHostToDevice, st)) ||
+      bad(cudaMemcpyAsync(sc + kStaticOffDstTable, h_dst_table, n * sizeof(int), cudaMemcpyHostToDevice, st)) ||
+      bad(cudaMemsetAsync(sc + kStaticOffWords, 0, 256, st)))
+    return KVX_ECUDA;
+
+  XferParams p{};
+  p.src.bases = reinterpret_cast<const unsigned long long*>(sc + kStaticOffSrcBases);
+  p.src.table = reinterpret_cast<const int*>(sc + kStaticOffSrcTable);
+  p.src.block_stride = s_stride;
+  p.src.num_blocks = src->num_blocks;
+  p.src.slice_off = pl.s_slice_off;
+  p.src.piece_stride = pl.s_piece_stride;
+  p.dst.bases = reinterpret_cast<const unsigned long long*>(sc + kStaticOffDstBases);
+  p.dst.table = reinterpret_cast<const int*>(sc + kStaticOffDstTable);
+  p.dst.block_stride = d_stride;
+  p.dst.num_blocks = dst->num_blocks;
+  p.dst.slice_off = pl.d_slice_off;
+  p.dst.piece_stride = pl.d_piece_stride;
+  p.total_items = static_cast<uint32_t>(total);
+  p.n = n; p.regions = src->regions; p.ppc = pl.ppc; p.piece_bytes = pl.piece_bytes;
+  p.s_runs = pl.s_runs; p.s_run_bytes = pl.s_run_bytes; p.s_stride = pl.s_stride;
+  p.d_runs = pl.d_runs; p.d_run_bytes = pl.d_run_bytes; p.d_n1 = pl.d_n1;
+  p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
+  p.stages = kStaticStages; p.stage_bytes = kStaticStageBytes;
+  p.flag = reinterpret_cast<unsigned long long*>(flag);
+  p.flag_val = flag_val;
+  p.done_counter = reinterpret_cast<unsigned int*>(sc + kStaticOffWords);
+  p.status = reinterpret_cast<unsigned int*>(sc + kStaticOffWords + 4);
+
+  const uint32_t grid = std::min<uint32_t>(static_cast<uint32_t>(dev->sms) * kStaticCtasPerSm, p.total_items);
+  kvx::kvx_xfer_tma_kernel<16, 8><<<grid, 32u * (1u + kStaticConsumerWarps), kStaticStages * kStaticStageBytes, st>>>(p);
+  if (bad(cudaGetLastError())) return KVX_ECUDA;
+  return KVX_OK;
+}

@@ -61,6 +61,7 @@ PROTOTYPES = {
     "kvx_scatter": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp]),
     "kvx_handoff_fused": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp]),
     "kvx_handoff_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp, c_vp]),
+    "kvx_handoff_static": (c_i32, [c_i32, P(PoolDesc), c_vp, P(PoolDesc), c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp]),
 }
 
 _lib = None

@@ -229,3 +229,30 @@ class Context:
         self._check(self.lib.kvx_handoff_host(self.handle, src.handle, _ptr(h_src_table), dst.handle,
                                               _ptr(h_dst_table), n, ctypes.byref(x) if x else None, flag, flag_val,
                                               _ptr(h_done), _stream(stream)), "kvx_handoff_host")
+
+
+STATIC_MAX_BLOCKS = 4096
+STATIC_MAX_REGIONS = 512
+
+
+def pool_desc(bases: Sequence[int], *, num_blocks: int, heads: int, head_dim: int, layout: int, block_tokens: int = 16,
+              elem_bytes: int = 2, block_stride: int = 0, tp_rank: int = 0, tp_size: int = 1):
+    """A kvx_pool_desc for entry points that take descriptors rather than registered pools.  Returns
+    (desc, keepalive): keep `keepalive` referenced for as long as `desc` is in use."""
+    arr = (c_vp * len(bases))(*[int(b) for b in bases])
+    d = PoolDesc(ctypes.sizeof(PoolDesc), len(bases), block_tokens, heads, head_dim, elem_bytes, layout, tp_rank,
+                 tp_size, 0, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
+    return d, arr
+
+
+def handoff_static(device: int, src_desc, h_src_table, dst_desc, h_dst_table, n: int, xf: Optional[Xform] = None,
+                   flag: Optional[int] = None, flag_val: int = 1, stream=None) -> int:
+    """kvx_handoff_static: the fused handoff for callers that may not allocate device memory (engines
+    whose HBM is fully budgeted to the KV pool, request-path threads that must not trigger
+    cudaMalloc's device-wide synchronisation).  No context, no registered pools: descriptors and host
+    block-id lists in, return code out (0 = launched).  At most STATIC_MAX_BLOCKS blocks and
+    STATIC_MAX_REGIONS regions per call; calls on one device must not overlap on the GPU."""
+    x = xf.c() if xf else None
+    return _lib.load().kvx_handoff_static(device, ctypes.byref(src_desc), _ptr(h_src_table), ctypes.byref(dst_desc),
+                                          _ptr(h_dst_table), n, ctypes.byref(x) if x else None, flag, flag_val,
+                                          _stream(stream))

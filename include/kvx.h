@@ -181,6 +181,42 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
                          const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, uint64_t* h_done,
                          void* stream);
 
+/*
+ * kvx_handoff_static — the fused handoff for callers that must not allocate.  It has no
+ * counterpart in the reference or in the transfer agent its images use; it exists because some
+ * users of this library cannot call cudaMalloc on the request path:
+ *   - a serving engine that gave every free byte of HBM to its KV pool at start-up (the usual
+ *     "GPU memory utilisation" budget), so a later cudaMalloc can fail or push it over budget;
+ *   - a scheduler thread for which cudaMalloc/cudaFree are off limits because they synchronise the
+ *     whole device and would stall decode steps running on other streams;
+ *   - a process whose allocator has been frozen or is metered by a quota layer.
+ * Such a caller has no kvx_ctx either (creating one allocates), so this entry takes the device
+ * ordinal and the two pool descriptors directly.  Everything the kernel needs beyond the caller's
+ * pools, tables and flag — device copies of the region base addresses and of both block tables,
+ * the finished-CTA counter and a status word — lives in one fixed array inside the library
+ * (KVX_STATIC_SCRATCH_BYTES of device memory, held by every GPU that loads libkvx.so until the
+ * process exits).  The call performs no cudaMalloc, cudaFree or other allocating call.
+ *
+ * Limits: n <= KVX_STATIC_MAX_BLOCKS and src/dst regions <= KVX_STATIC_MAX_REGIONS, otherwise the
+ * call returns KVX_ERANGE and launches nothing.  Block ids are checked against num_blocks
+ * (KVX_ERANGE).  Tables are HOST pointers; `flag` (device memory, may be NULL) receives flag_val
+ * when every byte has landed.
+ *
+ * One-time set-up: the first call on each device looks up the array's device address and prepares
+ * the kernel.  Make that first call before starting any stream capture on that device.
+ *
+ * Sharing: every call on a device uses the same array, which still holds the previous call's
+ * tables; the call re-uploads what it reads and clears the counter and status word itself.  Two
+ * calls that can overlap on the GPU (different streams, or different host threads) race on it:
+ * issue them on one stream, or order them with events.
+ */
+#define KVX_STATIC_MAX_BLOCKS 4096u
+#define KVX_STATIC_MAX_REGIONS 512u
+#define KVX_STATIC_SCRATCH_BYTES (2u * KVX_STATIC_MAX_REGIONS * 8u + 2u * KVX_STATIC_MAX_BLOCKS * 4u + 256u)
+int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, const int32_t* h_src_table,
+                           const kvx_pool_desc* dst, const int32_t* h_dst_table, uint32_t n,
+                           const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
