@@ -1,0 +1,101 @@
+"""Two-process P→D check (run under torchrun, world_size 2).  Rank 0 = prefill worker on GPU 0, rank 1 =
+decode worker on GPU 1 (or both on GPU 0 when only one device is visible).  The decode rank verifies the
+bytes that landed against the oracle.  With --cpu-dry-run no GPU is touched: only the control records
+travel (gloo), which is what the CPU test exercises."""
+import argparse
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "dynamo-k8s-llm-inference_b200"))
+
+from oracle import kvx_oracle as o  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cpu-dry-run", action="store_true")
+    ap.add_argument("--p-tp", type=int, default=1)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from kvx.shapes import KVShape
+    from kvx.tp import plan_edges
+    from kvx.workers import BlockAllocator, TransferParams, align_tables
+
+    shape = KVShape("test", 2, 8, 64)
+    n, nb_p, nb_d = 21, 40, 50
+    # control plane: decode allocates, prefill announces its block ids (kv_transfer_params)
+    if rank == 0:
+        alloc = BlockAllocator(nb_p, seed=5)
+        src_ids = alloc.allocate("req-0", n)
+        params = TransferParams("req-0", src_ids, 0, 1)
+    else:
+        alloc = BlockAllocator(nb_d, seed=6)
+        dst_ids = alloc.allocate("req-0", n - 4)  # partial prefix hit: 4 blocks already cached on D
+        params = None
+    box = [params]
+    dist.broadcast_object_list(box, src=0)
+    params = box[0]
+    if args.cpu_dry_run:
+        if rank == 1:
+            s, d = align_tables(params.remote_block_ids, dst_ids)
+            assert len(s) == len(d) == n - 4 and np.array_equal(s, params.remote_block_ids[4:])
+            assert 0 not in d and len(set(d.tolist())) == len(d)
+        edges = plan_edges(4, 2, 8)
+        assert [(e.p_rank, e.d_rank, e.dst_head_off) for e in edges] == [(0, 0, 0), (1, 0, 2), (2, 1, 0), (3, 1, 2)]
+        dist.barrier()
+        print(f"rank {rank} dry-run ok")
+        dist.destroy_process_group()
+        return
+
+    import kvx
+    from kvx import synth
+    from kvx.workers import DecodeWorker, PrefillWorker
+
+    dev = rank % torch.cuda.device_count()
+    torch.cuda.set_device(dev)
+    src_host = o.make_pool(shape.layers, 8, 64, nb_p, o.HND, seed=77)
+    if rank == 0:
+        w = PrefillWorker(dev, shape, nb_p, kvx.HND)
+        synth.upload(w.kv, src_host.buf)
+        metas = [None, None]
+    else:
+        w = DecodeWorker(dev, shape, nb_d, kvx.NHD)
+        synth.fill_canary(w.kv)
+        w.expect(3)
+        torch.cuda.synchronize()
+        metas = [None, w.metadata()]
+    got = [None, None]
+    dist.all_gather_object(got, metas[rank])
+    ids = [None]
+    if rank == 1:
+        ids = [dst_ids]
+    dist.broadcast_object_list(ids, src=1)
+    if rank == 0:
+        w.add_remote(0, got[1])
+        w.push(0, params.remote_block_ids, ids[0], slot=3, value=9)
+        torch.cuda.synchronize()
+        w.ctx.check()
+    dist.barrier()
+    if rank == 1:
+        w.wait(3, 9, 5000)
+        torch.cuda.synchronize()
+        w.ctx.check()
+        assert w.poll(3, 9)
+        want = o.make_pool(shape.layers, 8, 64, nb_d, o.NHD, fill="canary")
+        o.handoff(src_host, params.remote_block_ids, want, dst_ids)
+        assert np.array_equal(w.kv.to_numpy(), want.buf), "bytes landed on the decode GPU differ from the oracle"
+        print("pair ok")
+    dist.barrier()
+    w.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
