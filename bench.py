@@ -8,8 +8,9 @@ A step = one request's handoff (all layers, K and V) from a prefill pool to a de
   N = 1   config #2: Qwen3-0.6B KV shape, ISL 8192 (896 MiB payload), both pools on the one GPU
           (intra-device gather→transform→scatter, fused kernel), HND → NHD in flight.
   N = 2,4,8  configs #3/#5: Llama-3.1-8B KV shape, ISL 8192 (1 GiB payload), N/2 independent
-          P→D pairs; rank i (< N/2) is prefill worker i and pushes into decode worker N/2+i over
-          NVLink.  No collective on the data path ("scaling": "weak").
+          P→D pairs; rank i (< N/2) is prefill worker i, rank N/2+i its decode worker, which PULLS
+          the blocks over NVLink (--mode push: the prefill GPU stores them instead).  No collective
+          on the data path ("scaling": "weak").
 value = payload GB/s of the whole job (all pairs), inputs resident in HBM; e2e = the same through
 kvx_handoff_host with host block-id lists (H2D of the tables and D2H of the completion word inside
 the timed region).  --impl reference times the CPU memcpy handoff (oracle/kvx_oracle.c) instead.
@@ -244,6 +245,14 @@ def run_single(args):
     clocks = sampler.stop()
     ctx.check()
 
+    if args.no_extras:
+        ms_step = ms / args.steps
+        print(json.dumps({"metric": METRIC, "value": round(payload / (ms_step / 1e3) / 1e9, 2), "unit": UNIT, "n_gpus": 1,
+                          "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+                          "gpu_launches": int(launches), "clocks": clocks, "note": "--no-extras profiling run"}))
+        P.free(); D.free(); ctx.close()
+        return 0
+
     # the staged variant's kernels, each against the HBM roofline (2B bytes per launch)
     stage = torch.empty(payload, dtype=torch.uint8, device="cuda")
     stage2 = torch.empty(payload, dtype=torch.uint8, device="cuda")
@@ -353,30 +362,37 @@ def run_pairs(args):
     else:
         w = DecodeWorker(local, shape, nb, kvx.NHD, seed=rank)
         synth.fill_canary(w.kv)
+    w.expect(0)
+    w.expect(1)
+    torch.cuda.synchronize()
     metas = [None] * world
-    dist.all_gather_object(metas, w.metadata() if not is_p else None)
+    dist.all_gather_object(metas, w.metadata())
+    w.add_remote(0, metas[peer])
     perm_p = synth.make_table(nb, sets * n, synth.SEED_BASE + 3007 + (rank if is_p else peer))
     perm_d = synth.make_table(nb, sets * n, synth.SEED_BASE + 3013 + (peer if is_p else rank))
     total_steps = args.warmup + args.steps
-    launches = 0
-    e2e_s = 0.0
+    h_src = [np.ascontiguousarray(perm_p[s * n:(s + 1) * n]) for s in range(sets)]
+    h_dst = [np.ascontiguousarray(perm_d[s * n:(s + 1) * n]) for s in range(sets)]
+    d_src = [torch.from_numpy(t).cuda() for t in h_src]
+    d_dst = [torch.from_numpy(t).cuda() for t in h_dst]
+    pin_src = [torch.from_numpy(t).pin_memory() for t in h_src]
+    pin_dst = [torch.from_numpy(t).pin_memory() for t in h_dst]
+    pull = args.mode == "pull"
     clocks = None
-    if is_p:
-        w.add_remote(0, metas[peer])
-        h_src = [np.ascontiguousarray(perm_p[s * n:(s + 1) * n]) for s in range(sets)]
-        h_dst = [np.ascontiguousarray(perm_d[s * n:(s + 1) * n]) for s in range(sets)]
-        d_src = [torch.from_numpy(t).cuda() for t in h_src]
-        d_dst = [torch.from_numpy(t).cuda() for t in h_dst]
-        pin_src = [torch.from_numpy(t).pin_memory() for t in h_src]
-        pin_dst = [torch.from_numpy(t).pin_memory() for t in h_dst]
+    mover = (not is_p) if pull else is_p  # the rank whose GPU runs the transfer kernel
 
-        def step(k):
-            w.push(0, d_src[k % sets], d_dst[k % sets], slot=0, value=k + 1, host_tables=False, stream=stream)
-    else:
-        w.expect(0)
-        w.expect(1)
+    def move(k, slot, value, host, h_done=None):
+        s = k % sets
+        src, dst = (pin_src[s], pin_dst[s]) if host else (d_src[s], d_dst[s])
+        if pull:
+            w.pull(0, src, dst, notify_slot=slot, value=value, host_tables=host, h_done=h_done, stream=stream)
+        else:
+            w.push(0, src, dst, slot=slot, value=value, host_tables=host, h_done=h_done, stream=stream)
 
-        def step(k):
+    def step(k):
+        if mover:
+            move(k, 0, k + 1, False)
+        else:  # the other side only learns about completion through its flag
             w.wait(0, k + 1, 10000, stream)
 
     torch.cuda.synchronize()
@@ -398,21 +414,18 @@ def run_pairs(args):
     dist.barrier()
     w.ctx.check()
 
-    # e2e through the host-table entry (P side) / host poll of the flag (D side)
+    # e2e through the host-table entry on the moving side; the other side waits on its flag
     base = 100000
     done = torch.zeros(total_steps, dtype=torch.int64).pin_memory()
     torch.cuda.synchronize()
     dist.barrier()
     t0 = time.perf_counter()
-    if is_p:
-        for k in range(args.steps):
-            w.push(0, pin_src[k % sets], pin_dst[k % sets], slot=1, value=base + k + 1, host_tables=True,
-                   h_done=done[k:k + 1], stream=stream)
-        torch.cuda.synchronize()
-    else:
-        for k in range(args.steps):
+    for k in range(args.steps):
+        if mover:
+            move(k, 1, base + k + 1, True, done[k:k + 1])
+        else:
             w.wait(1, base + k + 1, 10000, stream)
-        torch.cuda.synchronize()
+    torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     dist.barrier()
     w.ctx.check()
@@ -449,15 +462,16 @@ def run_pairs(args):
             "per_pair_GBps": round(per_pair, 2), "pct_of_nvlink_900": round(100 * per_pair / 900.0, 2),
             "e2e": {"value": round(pairs * args.steps * payload / (e2e_ms / 1e3) / 1e9, 2), "unit": UNIT,
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8, "ms_per_step": round(e2e_ms / args.steps, 4),
-                    "through": "PrefillWorker.push -> kvx_handoff_host (host block-id lists, completion word back)"},
+                    "through": f"{'DecodeWorker.pull' if pull else 'PrefillWorker.push'} -> kvx_handoff_host (host block-id "
+                               "lists in, completion word back; release flag stored in the peer's memory)"},
             "gpu_launches": int(lt[0]), "clocks": clocks,
             "roofline": {"bound": "nvlink", "achieved": round(per_pair, 1), "peak": NVLINK_PEAK, "unit": "GB/s",
                          "frac": round(per_pair / NVLINK_PEAK, 4), "traffic": None,
                          "peak_source": "measured peer copy 770 GB/s per direction (B200_PROFILING.md); nominal 900",
-                         "kernel": "kvx_xfer_tma_kernel (fused gather+transform+peer store)",
+                         "kernel": "kvx_xfer_tma_kernel (fused: " + ("peer gather over NVLink + transform + local scatter, run by the decode GPU)" if pull else "local gather + transform + peer store, run by the prefill GPU)"),
                          "algorithmic_bytes_per_launch": payload, "frac_of_nominal_900": round(per_pair / 900.0, 4)},
             "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-            "landed_ok": bool(ok[0] > 0),
+            "direction": args.mode, "landed_ok": bool(ok[0] > 0),
         }
         print(json.dumps(line))
     dist.barrier()
@@ -473,6 +487,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="kvx", choices=["kvx", "reference"])
     ap.add_argument("--isl", type=int, default=8192)
+    ap.add_argument("--no-extras", action="store_true", help="N=1: skip the per-kernel table, ISL sweep and CPU baseline (profiling runs)")
+    ap.add_argument("--mode", default="pull", choices=["pull", "push"],
+                    help="N>1: decode GPU reads the prefill pool (pull, default) or prefill GPU stores into the decode pool")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup) if args.impl == "kvx" else args.warmup
     if args.impl == "reference":

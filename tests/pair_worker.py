@@ -64,33 +64,51 @@ def main():
     if rank == 0:
         w = PrefillWorker(dev, shape, nb_p, kvx.HND)
         synth.upload(w.kv, src_host.buf)
-        metas = [None, None]
     else:
         w = DecodeWorker(dev, shape, nb_d, kvx.NHD)
         synth.fill_canary(w.kv)
-        w.expect(3)
-        torch.cuda.synchronize()
-        metas = [None, w.metadata()]
+    w.expect(3)
+    torch.cuda.synchronize()
     got = [None, None]
-    dist.all_gather_object(got, metas[rank])
-    ids = [None]
-    if rank == 1:
-        ids = [dst_ids]
+    dist.all_gather_object(got, w.metadata())
+    w.add_remote(0, got[1 - rank])
+    ids = [dst_ids if rank == 1 else None]
     dist.broadcast_object_list(ids, src=1)
+    want = o.make_pool(shape.layers, 8, 64, nb_d, o.NHD, fill="canary")
+    o.handoff(src_host, params.remote_block_ids, want, ids[0])
+
+    # 1) pull: the decode rank reads the prefill pool over IPC/NVLink and releases the blocks
+    if rank == 1:
+        w.pull(0, params.remote_block_ids, dst_ids, notify_slot=3, value=9)
+        torch.cuda.synchronize()
+        w.ctx.check()
+        assert np.array_equal(w.kv.to_numpy(), want.buf), "pull: bytes on the decode GPU differ from the oracle"
+        print("pull ok")
+    dist.barrier()
     if rank == 0:
-        w.add_remote(0, got[1])
-        w.push(0, params.remote_block_ids, ids[0], slot=3, value=9)
+        w.wait(3, 9, 5000)  # release notification written by the decode rank's kernel
+        torch.cuda.synchronize()
+        w.ctx.check()
+        assert w.poll(3, 9)
+        alloc.free("req-0")  # every consumer released the blocks: give them back
+    dist.barrier()
+
+    # 2) push: same bytes the other way round (prefill GPU stores into the decode pool)
+    if rank == 1:
+        synth.fill_canary(w.kv)
+        w.expect(4)
+        torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:
+        w.push(0, params.remote_block_ids, ids[0], slot=4, value=11)
         torch.cuda.synchronize()
         w.ctx.check()
     dist.barrier()
     if rank == 1:
-        w.wait(3, 9, 5000)
+        w.wait(4, 11, 5000)
         torch.cuda.synchronize()
         w.ctx.check()
-        assert w.poll(3, 9)
-        want = o.make_pool(shape.layers, 8, 64, nb_d, o.NHD, fill="canary")
-        o.handoff(src_host, params.remote_block_ids, want, dst_ids)
-        assert np.array_equal(w.kv.to_numpy(), want.buf), "bytes landed on the decode GPU differ from the oracle"
+        assert np.array_equal(w.kv.to_numpy(), want.buf), "push: bytes on the decode GPU differ from the oracle"
         print("pair ok")
     dist.barrier()
     w.close()

@@ -1,0 +1,161 @@
+"""Outer boundary kept from the reference: the run-benchmarks.sh flag surface and the manifest-driven
+prefill/decode topology."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+from conftest import ROOT
+
+RUNNER = os.path.join(ROOT, "run-benchmarks.sh")
+
+DISAGG = """
+apiVersion: nvidia.com/v1alpha1
+kind: DynamoGraphDeployment
+metadata: {name: t-disagg}
+spec:
+  services:
+    Frontend: {componentType: frontend, replicas: 1}
+    Dec:
+      componentType: worker
+      subComponentType: decode
+      replicas: 2
+      resources: {limits: {gpu: "2"}}
+      extraPodSpec:
+        mainContainer:
+          image: example/sglang-runtime:1
+          command: [python3, -m, dynamo.sglang]
+          args: [--model-path, meta-llama/Llama-3.1-70B, --page-size, "16", --tp, "2", --disaggregation-mode, decode]
+    Pre:
+      componentType: worker
+      replicas: 1
+      resources: {limits: {gpu: "4"}}
+      extraPodSpec:
+        mainContainer:
+          command: [python3, -m, dynamo.vllm]
+          args: [--model, meta-llama/Llama-3.1-70B, --is-prefill-worker, --tensor-parallel-size=4]
+"""
+
+
+def _run(*args):
+    return subprocess.run([RUNNER, *args], capture_output=True, text=True)
+
+
+def test_usage_and_exit_codes_match_reference_runner():
+    r = _run("-h")
+    assert r.returncode == 0 and r.stderr.startswith("Usage: run-benchmarks.sh -u <api-url> -m <model> -o <output-dir> -b <benchmark-name>")
+    assert r.stdout == ""
+    r = _run("-u", "kvx://local", "-m", "Qwen/Qwen3-0.6B")
+    assert r.returncode == 1 and r.stderr.startswith("Missing required options.\nUsage:")
+    r = _run("-q")
+    assert r.returncode == 1 and r.stderr.startswith("Unknown option: -q\nUsage:")
+    r = _run("-u", "a", "-m")
+    assert r.returncode == 1 and r.stderr.startswith("Missing value for -m\nUsage:")
+    r = _run()
+    assert r.returncode == 1 and "Missing required options." in r.stderr
+
+
+def test_bad_endpoint_and_model_fail_cleanly(tmp_path):
+    r = _run("-u", "http://10.0.0.1:30080", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "x")
+    assert r.returncode == 1 and "unsupported endpoint scheme" in r.stderr
+    r = _run("-u", "kvx://local", "-m", "no/such-model", "-o", str(tmp_path), "-b", "x")
+    assert r.returncode == 1 and "unknown model" in r.stderr
+
+
+def test_getopts_semantics():
+    from kvx.cli import parse_args
+
+    assert parse_args(["-ukvx://l", "-m", "M", "-o", "O", "-b", "B", "-p"])[0] == ("kvx://l", "M", "O", "B", True)
+    assert parse_args(["-pu", "U", "-m", "M", "-o", "O", "-b", "B"])[0] == ("U", "M", "O", "B", True)
+    assert parse_args(["-u", "U", "-m", "M", "-o", "O", "-b", "B", "extra", "-p"])[0] == ("U", "M", "O", "B", False)
+
+
+def test_manifest_topology(tmp_path):
+    from kvx import HND, NHD
+    from kvx.manifest import load_manifest
+    from kvx.harness import rank_plans
+
+    p = tmp_path / "m.yaml"
+    p.write_text(DISAGG)
+    t = load_manifest(str(p))
+    assert t.disaggregated and t.name == "t-disagg" and t.gpus_needed() == 8
+    dec, pre = t.role("decode")[0], t.role("prefill")[0]
+    assert (dec.replicas, dec.gpus, dec.tp, dec.page_size, dec.backend, dec.layout) == (2, 2, 2, 16, "sglang", NHD)
+    assert (pre.replicas, pre.gpus, pre.tp, pre.backend, pre.layout, pre.model) == (1, 4, 4, "vllm", HND, "meta-llama/Llama-3.1-70B")
+    plans = rank_plans(t, 8)
+    assert [(x.role, x.replica, x.tp_rank, x.device) for x in plans] == [
+        ("prefill", 0, 0, 0), ("prefill", 0, 1, 1), ("prefill", 0, 2, 2), ("prefill", 0, 3, 3),
+        ("decode", 0, 0, 4), ("decode", 0, 1, 5), ("decode", 1, 0, 6), ("decode", 1, 1, 7)]
+    (tmp_path / "bad.yaml").write_text("kind: ConfigMap\n")
+    with pytest.raises(ValueError):
+        load_manifest(str(tmp_path / "bad.yaml"))
+
+
+def test_reference_manifests_if_present():
+    """The reference's own disagg manifests parse to 1 prefill + 1 decode worker, one GPU each (only where
+    /root/reference is mounted; never on the GPU box)."""
+    base = "/root/reference/examples/deploy"
+    if not os.path.isdir(base):
+        pytest.skip("reference not mounted")
+    from kvx.manifest import load_manifest
+
+    for be in ("vllm", "sglang", "trtllm"):
+        t = load_manifest(f"{base}/{be}/disagg.yaml")
+        assert t.backend == be and t.disaggregated and t.gpus_needed() == 2
+        assert all(w.replicas == 1 and w.gpus == 1 and w.tp == 1 and w.page_size == 16 for w in t.workers)
+        assert not load_manifest(f"{base}/{be}/agg.yaml").disaggregated
+
+
+def test_build_job_from_url(tmp_path):
+    from kvx.cli import build_job
+
+    p = tmp_path / "m.yaml"
+    p.write_text(DISAGG)
+    topo, cfg = build_job(f"kvx://local?manifest={p}&isl=1024,4096&requests=9&concurrency=2&stages=3", "meta-llama/Llama-3.1-70B")
+    assert topo.name == "t-disagg" and len(cfg.isl) == 9 and set(cfg.isl) <= {1024, 4096} and cfg.concurrency == 2
+    assert cfg.options == {"stages": 3}
+    topo, cfg = build_job("kvx://local?prefill=4&decode=4&isl=8192&requests=3", "meta-llama/Llama-3.1-8B")
+    assert [w.replicas for w in topo.workers] == [4, 4] and cfg.isl == [8192] * 3
+
+
+def test_plots_from_results(tmp_path):
+    from kvx.plot import plot_dir
+
+    d = tmp_path / "bench"
+    d.mkdir()
+    res = {"summary": {"topology": {"name": "t"}}, "decode_ranks": [{"requests": [
+        {"isl": 1024, "throughput_GBps": 500.0, "time_to_first_token_added_ms": 0.3},
+        {"isl": 8192, "throughput_GBps": 780.0, "time_to_first_token_added_ms": 1.4}]}]}
+    (d / "results.json").write_text(json.dumps(res))
+    out = plot_dir(str(tmp_path))
+    assert len(out) == 2 and all(open(p).read().startswith("<svg") for p in out)
+
+
+@pytest.mark.gpu
+def test_runner_end_to_end_on_gpu(tmp_path):
+    """The whole outer path: runner flags → topology → worker processes → pull stream → results + plots."""
+    p = tmp_path / "m.yaml"
+    p.write_text(DISAGG.replace('replicas: 2', 'replicas: 1').replace('gpu: "2"', 'gpu: "1"').replace('"2", --disagg', '"1", --disagg')
+                 .replace('gpu: "4"', 'gpu: "1"').replace("--tensor-parallel-size=4", "--tensor-parallel-size=1")
+                 .replace("Llama-3.1-70B", "Llama-3.2-1B-Instruct"))
+    out = tmp_path / "results"
+    r = _run("-u", f"kvx://local?manifest={p}&isl=1024,2048&requests=6&concurrency=2", "-m", "meta-llama/Llama-3.2-1B-Instruct",
+             "-o", str(out), "-b", "deployment-kvx", "-p")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    res = json.load(open(out / "deployment-kvx" / "results.json"))
+    s = res["summary"]
+    assert s["requests"] == 6 and s["verified_bit_exact"] is True and s["prefill_blocks_released"] is True
+    assert os.path.exists(out / "deployment-kvx" / "throughput_GBps.svg")
+
+
+@pytest.mark.gpu
+def test_runner_tp_reshard_on_gpu(tmp_path):
+    """Config #4 in small: TP4 prefill → TP2 decode (ranks share GPUs when fewer than 6 are visible)."""
+    out = tmp_path / "results"
+    r = _run("-u", "kvx://local?prefill=1&decode=1&ptp=4&dtp=2&isl=512&requests=3&layout=nhd", "-m", "meta-llama/Llama-3.2-1B-Instruct",
+             "-o", str(out), "-b", "tp")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    s = json.load(open(out / "tp" / "results.json"))["summary"]
+    assert s["verified_bit_exact"] is True and s["ranks"] == 6

@@ -69,7 +69,7 @@ def test_two_process_handoff_over_ipc():
         pytest.skip("no GPU")
     r = _torchrun([], 29612)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert "pair ok" in r.stdout
+    assert "pull ok" in r.stdout and "pair ok" in r.stdout
 
 
 @pytest.mark.gpu
@@ -100,5 +100,14 @@ def test_in_process_peer_handoff():
     torch.cuda.synchronize(0); torch.cuda.synchronize(1)
     want = o.make_pool(2, 8, 128, 33, o.HND, fill="canary")
     o.handoff(src_host, ts, want, td)
+    assert np.array_equal(d.kv.to_numpy(), want.buf)
+    # and the pull direction into fresh slots, releasing the prefill blocks
+    synth.fill_canary(d.kv)
+    p.expect(1)
+    torch.cuda.synchronize(0); torch.cuda.synchronize(1)
+    d.add_remote(0, p.metadata())
+    d.pull(0, ts, td, notify_slot=1, value=6)
+    p.wait(1, 6, 5000)
+    torch.cuda.synchronize(0); torch.cuda.synchronize(1)
     assert np.array_equal(d.kv.to_numpy(), want.buf)
     p.close(); d.close()
