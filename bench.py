@@ -44,6 +44,24 @@ def load_peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused kernel, from the committed
+    ncu --set full capture of this same workload (profiles/); None when no capture is committed."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_fused_latest.json")) as f:
+            d = json.load(f)
+        tot = []
+        for l in d["launches"]:
+            v = 0.0
+            for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                num, unit = l[k].split()
+                v += float(num) * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+            tot.append(v)
+        return round(sum(tot) / len(tot)), d.get("report")
+    except Exception:
+        return None, None
+
+
 NVLINK_PEAK = 770.0  # measured peer copy per direction on this pool (B200_PROFILING.md); nominal 900
 
 
@@ -304,6 +322,7 @@ def run_single(args):
     ms_step = ms / args.steps
     value = payload / (ms_step / 1e3) / 1e9
     achieved = 2 * payload / (ms_step / 1e3) / 1e9
+    traffic, traffic_src = ncu_traffic() if isl == 8192 else (None, None)
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -315,8 +334,8 @@ def run_single(args):
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": hbm_peak, "unit": "GB/s",
-                     "frac": round(achieved / hbm_peak, 4), "traffic": None, "peak_source": peak_src,
-                     "kernel": "kvx_xfer_tma_kernel (fused gather+transform+scatter)",
+                     "frac": round(achieved / hbm_peak, 4), "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": peak_src, "kernel": "kvx_xfer_tma_kernel (fused gather+transform+scatter)",
                      "algorithmic_bytes_per_launch": 2 * payload, "frac_of_nominal_8TBps": round(achieved / 8000.0, 4)},
         "cpu_baseline": {"value": round(cpu_gbps, 3), "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
