@@ -197,6 +197,68 @@ def timed_loop(torch, stream, fn, steps):
     return start.elapsed_time(end)  # ms
 
 
+def library_baselines(torch, np, ctx, shape, P, D, perm_p, perm_d, n, nb, payload, stream, threads):
+    """Baselines timed in the same run: (i) what the reference's images do today
+    when layouts differ — land the raw blocks, then torch index_select -> permute -> index_copy_ per
+    layer tensor (vLLM kv_connector/utils.py:255-277); (ii) a CPU-staged handoff: gather -> D2H into
+    pinned memory -> host memcpy-per-row transform -> H2D -> scatter (the kv_buffer_device=cpu shape)."""
+    from oracle import kvx_oracle as o
+    from oracle import kvx_oracle_c as oc
+    import ctypes
+
+    N, H, Dh = shape.block_tokens, shape.kv_heads, shape.head_dim
+    words = N * H * Dh
+    src = P.tensor().view(torch.int16).view(shape.regions, nb, words)
+    dst = D.tensor().view(torch.int16).view(shape.regions, nb, words)
+    si = torch.from_numpy(perm_p[:n].astype(np.int64)).cuda()
+    di = torch.from_numpy(perm_d[:n].astype(np.int64)).cuda()
+
+    def torch_path(_k):
+        for r in range(shape.regions):
+            cache = dst[r].view(nb, N, H, Dh)
+            cache.view(nb, -1).index_copy_(0, di, src[r].index_select(0, si))       # raw landing of HND bytes
+            blocks = cache.index_select(0, di)                                      # receive-side permute
+            cache.index_copy_(0, di, blocks.reshape(n, H, N, Dh).permute(0, 2, 1, 3))
+
+    for k in range(2):
+        torch_path(k)
+    torch.cuda.synchronize()
+    t_torch = timed_loop(torch, stream, torch_path, 3) / 3
+
+    # CPU-staged: one request, three repetitions
+    stage_dev = torch.empty(shape.regions, n, words, dtype=torch.int16, device="cuda")
+    host_in = torch.empty(shape.regions, n, words, dtype=torch.int16).pin_memory()
+    host_out = torch.empty(shape.regions, n, words, dtype=torch.int16).pin_memory()
+    lib = oc.lib()
+    chunk = words * 2
+
+    def side(t, layout):
+        return oc._Side(None, None, t.data_ptr(), 0, 0, layout, H, 0)
+
+    times = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        torch.index_select(src, 1, si, out=stage_dev)
+        host_in.copy_(stage_dev, non_blocking=True)
+        torch.cuda.synchronize()
+        s_side, d_side = side(host_in, o.HND), side(host_out, o.NHD)
+        rc = lib.kvxo_xfer(ctypes.byref(s_side), ctypes.byref(d_side), shape.regions, n, N, H, Dh * 2, threads)
+        assert rc == 0
+        stage_dev.copy_(host_out, non_blocking=True)
+        dst.index_copy_(1, di, stage_dev)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+    t_cpu = min(times)
+    del stage_dev
+    return {
+        "torch_land_then_index_select_permute_index_copy": {"ms": round(t_torch, 3), "payload_GBps": round(payload / t_torch / 1e6, 1),
+                                                            "launches_per_request": 5 * shape.regions},
+        "cpu_staged_d2h_hostmemcpy_h2d": {"ms": round(1e3 * t_cpu, 2), "payload_GBps": round(payload / t_cpu / 1e9, 2),
+                                          "host_threads": threads, "sample": "1 request x 3 repetitions, best"},
+    }
+
+
 def run_single(args):
     import numpy as np
     import torch
@@ -317,6 +379,7 @@ def run_single(args):
                              "hbm_frac_measured": round(2 * b / (t / 1e3) / 1e9 / hbm_peak, 4)}
 
     threads = len(os.sched_getaffinity(0))
+    baselines = library_baselines(torch, np, ctx, shape, P, D, perm_p, perm_d, n, nb, payload, stream, threads)
     cpu_gbps, cpu_reps, _, _ = cpu_handoff_rate(shape, isl, min_seconds=10.0, max_reps=200, threads=threads)
 
     ms_step = ms / args.steps
@@ -341,7 +404,7 @@ def run_single(args):
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
                                    "oracle/kvx_oracle.c memcpy-per-row HND->NHD"},
         "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-        "kernels": parts, "isl_sweep": sweep,
+        "kernels": parts, "isl_sweep": sweep, "baselines": baselines,
         "options": {k: ctx.get_option(k) for k in kvx.OPT},
     }
     print(json.dumps(line))
