@@ -233,7 +233,7 @@ def library_baselines(torch, np, ctx, shape, P, D, perm_p, perm_d, n, nb, payloa
     chunk = words * 2
 
     def side(t, layout):
-        return oc._Side(None, None, t.data_ptr(), 0, 0, layout, H, 0)
+        return oc._Side(None, None, t.data_ptr(), 0, 0, layout, H, 0, 0)
 
     times = []
     for _ in range(3):

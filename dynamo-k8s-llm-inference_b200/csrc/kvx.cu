@@ -114,22 +114,26 @@ int64_t env_or(const char* name, int64_t dflt) {
 }
 
 // ---- geometry ---------------------------------------------------------------------------------
-struct ChunkGeom {  // one side's chunk: H heads in `layout`, slice starts at head `off`
-  uint32_t layout, heads, off;
+struct ChunkGeom {  // one side's chunk: H heads in `layout`, slice starts at head `off`, nb tokens per block
+  uint32_t layout, heads, off, nb;
 };
 
 struct Plan {
   uint32_t ppc, piece_bytes;
-  uint32_t s_runs, s_run_bytes, s_stride, s_slice_off, s_piece_stride;
-  uint32_t d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b, d_slice_off, d_piece_stride;
+  uint32_t s_runs, s_run_bytes, s_stride, s_slice_off, s_piece_stride, s_sub_stride;
+  uint32_t d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b, d_slice_off, d_piece_stride, d_sub_stride;
 };
 
-// Split a slice of Hc heads x N tokens x R bytes into pieces of at most `cap` bytes and describe
-// each piece as source runs / destination runs (see XferParams).  Pieces split along the source's
-// major dimension (tokens for NHD, heads for HND) so that both sides stay a 2-level run pattern.
+// Split a slice of Hc heads x N tokens x R bytes (one GRANULE: N is the smaller of the two sides'
+// block sizes) into pieces of at most `cap` bytes and describe each piece as source runs /
+// destination runs (see XferParams).  Pieces split along the source's major dimension (tokens for
+// NHD, heads for HND) so that both sides stay a 2-level run pattern.  A side whose blocks hold
+// nb = k*N tokens keeps k granules per block: NHD granules are contiguous token ranges, HND
+// granules are N-row runs inside each head's nb rows (head stride nb*R).
 int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d, uint32_t cap, Plan* out) {
   if (Hc == 0 || N == 0 || R == 0 || (R % 16u) != 0) return KVX_EUNSUPPORTED;
   if (s.off + Hc > s.heads || d.off + Hc > d.heads) return KVX_EINVAL;
+  if (s.nb < N || d.nb < N || s.nb % N || d.nb % N) return KVX_EINVAL;
   const bool src_hnd = s.layout == KVX_LAYOUT_HND;
   const bool dst_hnd = d.layout == KVX_LAYOUT_HND;
   const uint32_t major = src_hnd ? Hc : N;
@@ -145,38 +149,37 @@ int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d,
   Plan p{};
   p.ppc = major / g;
   p.piece_bytes = g * unit_bytes;
+  p.s_sub_stride = src_hnd ? N * R : N * s.heads * R;
+  p.d_sub_stride = dst_hnd ? N * R : N * d.heads * R;
   if (src_hnd) {
-    // source slice [off, off+Hc) heads is contiguous: Hc * N * R bytes
-    p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0;
-    p.s_slice_off = s.off * N * R; p.s_piece_stride = g * N * R;
+    // image order (h, t); head h of the granule is N*R contiguous bytes, heads are s.nb*R apart
+    if (s.nb == N) { p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; }
+    else           { p.s_runs = g; p.s_run_bytes = N * R; p.s_stride = s.nb * R; }
+    p.s_slice_off = s.off * s.nb * R; p.s_piece_stride = g * s.nb * R;
     if (dst_hnd) {
-      p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; p.d_stride_b = 0;
-      p.d_slice_off = d.off * N * R; p.d_piece_stride = g * N * R;
+      if (d.nb == N) { p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; }
+      else           { p.d_runs = g; p.d_run_bytes = N * R; p.d_n1 = 1; p.d_stride_a = d.nb * R; }
+      p.d_stride_b = 0;
+      p.d_slice_off = d.off * d.nb * R; p.d_piece_stride = g * d.nb * R;
     } else {
       // image order (h, t) → NHD row (t, off+h): run x = h*N + t
       p.d_runs = g * N; p.d_run_bytes = R; p.d_n1 = N; p.d_stride_a = R; p.d_stride_b = d.heads * R;
       p.d_slice_off = d.off * R; p.d_piece_stride = g * R;
     }
   } else {
-    if (Hc == s.heads) {
-      p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; p.s_slice_off = 0;
-    } else {
-      p.s_runs = g; p.s_run_bytes = Hc * R; p.s_stride = s.heads * R; p.s_slice_off = s.off * R;
-    }
-    p.s_piece_stride = g * s.heads * R;
+    // image order (t, h); token t of the slice is Hc*R contiguous bytes, tokens are s.heads*R apart
+    if (Hc == s.heads) { p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; }
+    else               { p.s_runs = g; p.s_run_bytes = Hc * R; p.s_stride = s.heads * R; }
+    p.s_slice_off = s.off * R; p.s_piece_stride = g * s.heads * R;
     if (!dst_hnd) {
-      if (Hc == d.heads) {
-        p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; p.d_stride_b = 0;
-        p.d_slice_off = 0;
-      } else {
-        p.d_runs = g; p.d_run_bytes = Hc * R; p.d_n1 = 1; p.d_stride_a = d.heads * R; p.d_stride_b = 0;
-        p.d_slice_off = d.off * R;
-      }
-      p.d_piece_stride = g * d.heads * R;
+      if (Hc == d.heads) { p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; }
+      else               { p.d_runs = g; p.d_run_bytes = Hc * R; p.d_n1 = 1; p.d_stride_a = d.heads * R; }
+      p.d_stride_b = 0;
+      p.d_slice_off = d.off * R; p.d_piece_stride = g * d.heads * R;
     } else {
       // image order (t, h) → HND row (off+h, t): run x = t*Hc + h
-      p.d_runs = g * Hc; p.d_run_bytes = R; p.d_n1 = Hc; p.d_stride_a = R; p.d_stride_b = N * R;
-      p.d_slice_off = d.off * N * R; p.d_piece_stride = g * R;
+      p.d_runs = g * Hc; p.d_run_bytes = R; p.d_n1 = Hc; p.d_stride_a = R; p.d_stride_b = d.nb * R;
+      p.d_slice_off = d.off * d.nb * R; p.d_piece_stride = g * R;
     }
   }
   *out = p;
@@ -200,6 +203,7 @@ bool all_aligned(uint64_t a, const Plan& pl, const XferSide& s, const XferSide& 
   auto m = [a](uint64_t v) { return (v % a) == 0; };
   return m(pl.s_run_bytes) && m(pl.d_run_bytes) && m(pl.s_stride) && m(pl.d_stride_a) && m(pl.d_stride_b) &&
          m(pl.s_slice_off) && m(pl.d_slice_off) && m(pl.s_piece_stride) && m(pl.d_piece_stride) &&
+         m(pl.s_sub_stride) && m(pl.d_sub_stride) &&
          m(s.block_stride) && m(d.block_stride) && m(s.base0) && m(d.base0);
 }
 
@@ -262,7 +266,11 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     if (rc != KVX_OK) return rc;
     p.src.slice_off = pl.s_slice_off; p.src.piece_stride = pl.s_piece_stride;
     p.dst.slice_off = pl.d_slice_off; p.dst.piece_stride = pl.d_piece_stride;
+    p.src.ratio = ls.sg.nb / ls.N; p.src.sub_stride = pl.s_sub_stride;
+    p.dst.ratio = ls.dg.nb / ls.N; p.dst.sub_stride = pl.d_sub_stride;
   }
+  if (p.src.ratio == 0) p.src.ratio = 1;
+  if (p.dst.ratio == 0) p.dst.ratio = 1;
   const uint64_t total = static_cast<uint64_t>(p.n) * p.regions * pl.ppc;
   if (total == 0) {
     if (ls.flag) {  // empty request (full prefix hit): notify only
@@ -371,9 +379,16 @@ XferSide contiguous_side(const void* base, uint64_t chunk_bytes) {
   return s;
 }
 
+// Pools that can be joined by one transfer: same regions and row size; block sizes may differ by an
+// integer ratio (regrouped in flight).
 bool same_shape(const kvx_pool_desc& a, const kvx_pool_desc& b) {
-  return a.regions == b.regions && a.block_tokens == b.block_tokens && a.head_dim == b.head_dim &&
-         a.elem_bytes == b.elem_bytes;
+  const uint32_t lo = std::min(a.block_tokens, b.block_tokens), hi = std::max(a.block_tokens, b.block_tokens);
+  return a.regions == b.regions && lo != 0 && hi % lo == 0 && a.head_dim == b.head_dim && a.elem_bytes == b.elem_bytes;
+}
+
+uint32_t table_entries(uint32_t n, const kvx_pool_desc& side, const kvx_pool_desc& other) {
+  const uint32_t k = side.block_tokens / std::min(side.block_tokens, other.block_tokens);
+  return (n + k - 1) / k;
 }
 
 typedef CUresult (*PFN_cuMemGetAddressRange)(CUdeviceptr*, size_t*, CUdeviceptr);
@@ -808,8 +823,8 @@ int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, ui
   ls.dst = contiguous_side(staging, stage_chunk);
   ls.n = n; ls.regions = d.regions;
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{d.layout, d.heads, so};
-  ls.dg = ChunkGeom{sl, hc, 0};
+  ls.sg = ChunkGeom{d.layout, d.heads, so, d.block_tokens};
+  ls.dg = ChunkGeom{sl, hc, 0, d.block_tokens};
   return launch_xfer(ctx, ls, &src->base, nullptr, static_cast<cudaStream_t>(stream));
 }
 
@@ -828,8 +843,8 @@ int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, cons
   ls.dst = paged_side(dst, d_table);
   ls.n = n; ls.regions = d.regions;
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{sl, hc, 0};
-  ls.dg = ChunkGeom{d.layout, d.heads, dof};
+  ls.sg = ChunkGeom{sl, hc, 0, d.block_tokens};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
   return launch_xfer(ctx, ls, nullptr, &dst->base, static_cast<cudaStream_t>(stream));
 }
 
@@ -868,9 +883,10 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
   ls.src = paged_side(src, d_src_table);
   ls.dst = paged_side(dst, d_dst_table);
   ls.n = n; ls.regions = s.regions;
-  ls.N = s.block_tokens; ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{s.layout, s.heads, so};
-  ls.dg = ChunkGeom{d.layout, d.heads, dof};
+  ls.N = std::min(s.block_tokens, d.block_tokens);  // granule = the smaller block
+  ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
+  ls.sg = ChunkGeom{s.layout, s.heads, so, s.block_tokens};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
   ls.flag = flag;
   ls.flag_val = flag_val;
   return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
@@ -886,19 +902,20 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
   DeviceGuard guard(ctx->device);
   // The peer may own the destination blocks: ids are validated here against each pool's size so a
   // bad list never reaches the kernel (the kernel re-checks device-resident tables itself).
-  for (uint32_t i = 0; i < n; ++i) {
+  const uint32_t ns = table_entries(n, src->desc, dst->desc), nd = table_entries(n, dst->desc, src->desc);
+  for (uint32_t i = 0; i < ns; ++i)
     if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->desc.num_blocks) return KVX_ERANGE;
+  for (uint32_t i = 0; i < nd; ++i)
     if (h_dst_table[i] < 0 || static_cast<uint64_t>(h_dst_table[i]) >= dst->desc.num_blocks) return KVX_ERANGE;
-  }
   int* d_src = nullptr;
   int* d_dst = nullptr;
   if (n != 0) {
-    if (ctx->table_cursor + 2ull * n > kTableRing) ctx->table_cursor = 0;
+    if (ctx->table_cursor + static_cast<uint64_t>(ns) + nd > kTableRing) ctx->table_cursor = 0;
     d_src = ctx->d_table_ring + ctx->table_cursor;
-    d_dst = d_src + n;
-    ctx->table_cursor += 2 * n;
-    KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, n * sizeof(int), cudaMemcpyHostToDevice, st));
-    KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, n * sizeof(int), cudaMemcpyHostToDevice, st));
+    d_dst = d_src + ns;
+    ctx->table_cursor += ns + nd;
+    KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, ns * sizeof(int), cudaMemcpyHostToDevice, st));
+    KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, nd * sizeof(int), cudaMemcpyHostToDevice, st));
   }
   uint64_t* f = flag ? flag : ctx->d_flags + (kNumFlags - 1);
   int32_t rc = kvx_handoff_fused(ctx, src, d_src, dst, d_dst, n, xf, f, flag_val, stream);
@@ -998,6 +1015,7 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   rc = static_check_desc(dst, &d_chunk, &d_stride);
   if (rc) return rc;
   if (!same_shape(*src, *dst)) return KVX_EINVAL;
+  if (src->block_tokens != dst->block_tokens) return KVX_EUNSUPPORTED;  // no block-size regrouping here
   if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
   for (uint32_t i = 0; i < n; ++i) {
     if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->num_blocks) return KVX_ERANGE;
@@ -1027,8 +1045,9 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   }
 
   Plan pl{};
-  rc = make_plan(src->block_tokens, src->head_dim * src->elem_bytes, hc, ChunkGeom{src->layout, src->heads, so},
-                 ChunkGeom{dst->layout, dst->heads, dof}, kStaticStageBytes, &pl);
+  rc = make_plan(src->block_tokens, src->head_dim * src->elem_bytes, hc,
+                 ChunkGeom{src->layout, src->heads, so, src->block_tokens},
+                 ChunkGeom{dst->layout, dst->heads, dof, dst->block_tokens}, kStaticStageBytes, &pl);
   if (rc) return rc;  // a head/token unit larger than one 16 KiB stage is not supported here
   const uint64_t total = static_cast<uint64_t>(n) * src->regions * pl.ppc;
   if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;
@@ -1050,6 +1069,8 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   p.src.num_blocks = src->num_blocks;
   p.src.slice_off = pl.s_slice_off;
   p.src.piece_stride = pl.s_piece_stride;
+  p.src.ratio = 1;
+  p.dst.ratio = 1;
   p.dst.bases = reinterpret_cast<const unsigned long long*>(sc + kStaticOffDstBases);
   p.dst.table = reinterpret_cast<const int*>(sc + kStaticOffDstTable);
   p.dst.block_stride = d_stride;

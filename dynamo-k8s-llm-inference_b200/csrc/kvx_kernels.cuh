@@ -34,6 +34,8 @@ struct XferSide {
   unsigned long long num_blocks;    // paged: ids must be < num_blocks
   unsigned int slice_off;           // byte offset of the moved slice inside a chunk
   unsigned int piece_stride;        // bytes between consecutive pieces of one chunk
+  unsigned int ratio;               // paged: granules per block on this side (block-size regrouping), >= 1
+  unsigned int sub_stride;          // paged: bytes between consecutive granules inside one block
 };
 
 struct XferParams {
@@ -188,12 +190,14 @@ __device__ __forceinline__ unsigned long long side_addr(const XferSide& s, unsig
                                                         unsigned n, bool& ok) {
   unsigned long long a;
   if (s.bases != nullptr) {
-    const int id = s.table ? __ldg(s.table + i) : static_cast<int>(i);
+    const unsigned blk = i / s.ratio, sub = i % s.ratio;
+    const int id = s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
     if (id < 0 || static_cast<unsigned long long>(id) >= s.num_blocks) {
       ok = false;
       return 0;
     }
-    a = __ldg(s.bases + r) + static_cast<unsigned long long>(id) * s.block_stride;
+    a = __ldg(s.bases + r) + static_cast<unsigned long long>(id) * s.block_stride +
+        static_cast<unsigned long long>(sub) * s.sub_stride;
   } else {
     a = s.base0 + (static_cast<unsigned long long>(r) * n + i) * s.block_stride;
   }
@@ -224,9 +228,11 @@ __device__ __forceinline__ unsigned dst_run_offset(const XferParams& p, unsigned
 // flag (H6) and re-zeroes the counter for the next launch that gets this counter slot.
 __device__ __forceinline__ void finish_and_flag(const XferParams& p) {
   if (p.flag == nullptr) return;
-  __threadfence_system();
+  // bar.sync orders every thread's stores before thread 0's system-scope fence, which is cumulative
+  // (the pattern cooperative-groups grid sync uses): one fence per CTA instead of one per thread.
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence_system();
     const unsigned prev = atomicAdd(p.done_counter, 1u);
     if (prev == gridDim.x - 1) {
       __threadfence_system();

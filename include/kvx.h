@@ -166,7 +166,13 @@ int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, cons
                     uint32_t n, const kvx_xform* xf, void* stream);
 
 /* H1-H6 in one kernel: source blocks → shared memory → destination blocks (local or peer pool),
- * then the completion flag.  `flag` may be NULL. */
+ * then the completion flag.  `flag` may be NULL.  Either pool may be a peer's (imported): run it on
+ * the decode GPU with an imported source to PULL (reads cross NVLink), or on the prefill GPU with an
+ * imported destination to PUSH.
+ * Block-size regrouping: the two pools' block_tokens may differ by an integer ratio k (P 16-token
+ * blocks into D 32/64-token blocks, [vllm] kv_connector/utils.py:224-252,280-299, or the reverse).
+ * `n` then counts GRANULES = blocks of the smaller size; the other side's table holds ceil(n/k)
+ * ids and granule i occupies tokens [(i % k)*N, +N) of its block table[i / k]. */
 int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table,
                           const kvx_pool* dst, const int32_t* d_dst_table, uint32_t n,
                           const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);

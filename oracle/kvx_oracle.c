@@ -31,6 +31,7 @@ typedef struct kvxo_side {
   uint32_t layout;        /* row order of this side's chunk                                   */
   uint32_t heads;         /* heads in this side's chunk                                       */
   uint32_t head_off;      /* first head of the moved slice                                    */
+  uint32_t block_tokens;  /* tokens per block on THIS side (0 = the granule N)                */
 } kvxo_side;
 
 typedef struct kvxo_job {
@@ -41,18 +42,25 @@ typedef struct kvxo_job {
   int rc;
 } kvxo_job;
 
-static uint8_t* chunk_addr(const kvxo_side* s, uint32_t r, uint32_t i, uint32_t n, uint32_t N, uint32_t R, int* ok) {
+/* Block holding granule i.  With block_tokens = k*N the granule i is tokens [(i%k)*N, +N) of block
+ * table[i/k] (block-size regrouping, vLLM kv_connector/utils.py:224-252,280-299); *sub gets i%k. */
+static uint8_t* chunk_addr(const kvxo_side* s, uint32_t r, uint32_t i, uint32_t n, uint32_t N, uint32_t R, int* ok,
+                           uint32_t* sub) {
+  const uint32_t k = (s->block_tokens > N) ? s->block_tokens / N : 1;
+  *sub = i % k;
   if (s->base) {
-    int32_t id = s->table ? s->table[i] : (int32_t)i;
+    int32_t id = s->table ? s->table[i / k] : (int32_t)(i / k);
     if (id < 0 || (uint64_t)id >= s->num_blocks) { *ok = 0; return NULL; }
     return s->base[r] + (uint64_t)id * s->block_stride;
   }
   return s->base0 + ((uint64_t)r * n + i) * ((uint64_t)N * s->heads * R);
 }
 
-static inline uint64_t row_off(const kvxo_side* s, uint32_t t, uint32_t h, uint32_t N, uint32_t R) {
-  uint32_t hh = s->head_off + h;
-  return s->layout == KVXO_NHD ? ((uint64_t)t * s->heads + hh) * R : ((uint64_t)hh * N + t) * R;
+static inline uint64_t row_off(const kvxo_side* s, uint32_t sub, uint32_t t, uint32_t h, uint32_t N, uint32_t R) {
+  const uint32_t hh = s->head_off + h;
+  const uint32_t nb = (s->block_tokens > N) ? s->block_tokens : N; /* tokens per block on this side */
+  const uint32_t tt = sub * N + t;
+  return s->layout == KVXO_NHD ? ((uint64_t)tt * s->heads + hh) * R : ((uint64_t)hh * nb + tt) * R;
 }
 
 static void* worker(void* arg) {
@@ -61,13 +69,14 @@ static void* worker(void* arg) {
   for (uint64_t w = j->tid; w < items; w += j->threads) {
     const uint32_t r = (uint32_t)(w / j->n), i = (uint32_t)(w % j->n);
     int ok = 1;
-    const uint8_t* sc = chunk_addr(j->src, r, i, j->n, j->N, j->row_bytes, &ok);
-    uint8_t* dc = chunk_addr(j->dst, r, i, j->n, j->N, j->row_bytes, &ok);
+    uint32_t ssub = 0, dsub = 0;
+    const uint8_t* sc = chunk_addr(j->src, r, i, j->n, j->N, j->row_bytes, &ok, &ssub);
+    uint8_t* dc = chunk_addr(j->dst, r, i, j->n, j->N, j->row_bytes, &ok, &dsub);
     if (!ok) { j->rc = -6; continue; }
     for (uint32_t t = 0; t < j->N; ++t)
       for (uint32_t h = 0; h < j->Hc; ++h)
-        memcpy(dc + row_off(j->dst, t, h, j->N, j->row_bytes), sc + row_off(j->src, t, h, j->N, j->row_bytes),
-               j->row_bytes);
+        memcpy(dc + row_off(j->dst, dsub, t, h, j->N, j->row_bytes),
+               sc + row_off(j->src, ssub, t, h, j->N, j->row_bytes), j->row_bytes);
   }
   return NULL;
 }

@@ -240,6 +240,8 @@ def scatter(staging: np.ndarray, dst: Pool, table: Sequence[int], xf: Optional[X
 
 def handoff(src: Pool, src_table: Sequence[int], dst: Pool, dst_table: Sequence[int], xf: Optional[Xform] = None) -> None:
     """H1-H5 composed: what one P rank → D rank edge of a request does."""
+    if src.block_tokens != dst.block_tokens:
+        return handoff_regroup(src, src_table, dst, dst_table, xf)
     so, do, hc, _ = _resolve(xf, src.heads, dst.heads, src.layout)
     st_src, st_dst = list(src_table), list(dst_table)
     if len(st_dst) < len(st_src):
@@ -253,6 +255,38 @@ def handoff(src: Pool, src_table: Sequence[int], dst: Pool, dst_table: Sequence[
     image = gather(src, st_src, Xform(so, 0, hc, dst.layout))
     image = copy(image)
     scatter(image, dst, st_dst, Xform(0, do, hc, dst.layout))
+
+
+def handoff_regroup(src: Pool, src_table: Sequence[int], dst: Pool, dst_table: Sequence[int],
+                    xf: Optional[Xform] = None, n_small: Optional[int] = None) -> None:
+    """Handoff between pools whose block sizes differ by an integer ratio k (P 16-token blocks into
+    D 32/64-token blocks or the reverse).  The granule is the smaller block; granule i lives in big
+    block table[i // k] at tokens [(i % k) * N, +N).  This is the regrouping [vllm]
+    kv_connector/utils.py:224-252 (same layout) and :280-299 (HND → NHD) perform after landing k
+    remote blocks back to back in one local block.  n_small defaults to k * len(big table), capped by
+    the small side's table."""
+    so, do, hc, _ = _resolve(xf, src.heads, dst.heads, src.layout)
+    Ns, Nd = src.block_tokens, dst.block_tokens
+    N = min(Ns, Nd)
+    if max(Ns, Nd) % N:
+        raise ValueError("block sizes must divide")
+    ks, kd = Ns // N, Nd // N
+    ts, td = _check_table(src_table, src.num_blocks), _check_table(dst_table, dst.num_blocks)
+    if n_small is None:
+        n_small = min(len(ts) * ks, len(td) * kd)
+    if n_small > len(ts) * ks or n_small > len(td) * kd:
+        raise ValueError("tables too short for n_small granules")
+    R = src.row_bytes
+    for r in range(src.regions):
+        sview, dview = src.region_view(r), dst.region_view(r)
+        for i in range(n_small):
+            sb, ss = int(ts[i // ks]), i % ks
+            db, dsub = int(td[i // kd]), i % kd
+            srows = _rows(sview[sb : sb + 1], src.layout, Ns, src.heads, R)[0, ss * N : (ss + 1) * N, so : so + hc, :]
+            cur = dview[db : db + 1].copy()
+            drows = _rows(cur, dst.layout, Nd, dst.heads, R).copy()
+            drows[0, dsub * N : (dsub + 1) * N, do : do + hc, :] = srows
+            dview[db] = _pack(drows, dst.layout)[0]
 
 
 # ------------------------------------------------------------------------------------------------

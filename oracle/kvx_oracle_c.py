@@ -24,6 +24,7 @@ class _Side(ctypes.Structure):
         ("layout", ctypes.c_uint32),
         ("heads", ctypes.c_uint32),
         ("head_off", ctypes.c_uint32),
+        ("block_tokens", ctypes.c_uint32),
     ]
 
 
@@ -59,22 +60,25 @@ def _paged(pool: o.Pool, table: np.ndarray, head_off: int, keep: list) -> _Side:
         pool.layout,
         pool.heads,
         head_off,
+        pool.block_tokens,
     )
 
 
 def _contig(image: np.ndarray, layout: int, heads: int) -> _Side:
-    return _Side(None, None, image.ctypes.data, 0, 0, layout, heads, 0)
+    return _Side(None, None, image.ctypes.data, 0, 0, layout, heads, 0, 0)
 
 
 def handoff(src: o.Pool, src_table: Sequence[int], dst: o.Pool, dst_table: Sequence[int],
             xf: Optional[o.Xform] = None, threads: int = 1) -> int:
-    """Direct paged→paged move with the C loop (same semantics as kvx_oracle.handoff, equal-length tables)."""
+    """Direct paged→paged move with the C loop (same semantics as kvx_oracle.handoff, equal-length tables;
+    with unequal block sizes the granule is the smaller block, see kvx_oracle.handoff_regroup)."""
     so, do, hc, _ = o._resolve(xf, src.heads, dst.heads, src.layout)
     keep: list = []
     s = _paged(src, np.asarray(src_table), so, keep)
     d = _paged(dst, np.asarray(dst_table), do, keep)
-    return lib().kvxo_xfer(ctypes.byref(s), ctypes.byref(d), src.regions, len(src_table), src.block_tokens, hc,
-                           src.row_bytes, threads)
+    N = min(src.block_tokens, dst.block_tokens)
+    n = min(len(src_table) * (src.block_tokens // N), len(dst_table) * (dst.block_tokens // N))
+    return lib().kvxo_xfer(ctypes.byref(s), ctypes.byref(d), src.regions, n, N, hc, src.row_bytes, threads)
 
 
 def gather(src: o.Pool, table: Sequence[int], xf: Optional[o.Xform] = None, threads: int = 1) -> np.ndarray:

@@ -50,6 +50,45 @@ def layout_fixture():
     print("layout_hnd_to_nhd.npz written")
 
 
+def blocksize_fixture():
+    """P blocks of 4 tokens (HND) land in D blocks of 16 tokens: D kept HND
+    (kv_postprocess_blksize_on_receive, utils.py:224-252) and D in NHD
+    (kv_postprocess_blksize_and_layout_on_receive, utils.py:280-299)."""
+    from vllm.distributed.kv_transfer.kv_connector.utils import (
+        kv_postprocess_blksize_and_layout_on_receive, kv_postprocess_blksize_on_receive)
+
+    rng = np.random.Generator(np.random.PCG64(20261107))
+    L, H, D, Np, ratio = 1, 4, 8, 4, 4
+    Nd = Np * ratio
+    nb_p, nb_d, n_d = 40, 9, 3          # 3 decode blocks = 12 prefill blocks
+    n_p = n_d * ratio
+    regions = 2 * L
+    p = rng.integers(0, 65536, size=(regions, nb_p, H, Np, D), dtype=np.uint16)      # HND small blocks
+    p_table = (1 + rng.permutation(nb_p - 1)[:n_p]).astype(np.int32)
+    d_table = (1 + rng.permutation(nb_d - 1)[:n_d]).astype(np.int32)
+    idx = torch.from_numpy(d_table.astype(np.int64))
+    out = {}
+    for name in ("hnd", "nhd"):
+        d = np.full((regions, nb_d, Nd * H * D), 0xC0DE, dtype=np.uint16)
+        for r in range(regions):
+            flat = torch.from_numpy(d[r].view(np.int16))
+            # raw landing: the k prefill blocks of one decode block, back to back
+            src = torch.from_numpy(p[r].view(np.int16).reshape(nb_p, -1)[p_table.astype(np.int64)]).reshape(n_d, -1)
+            flat[idx] = src
+            if name == "hnd":
+                # logical view [nb, N, H, D] whose physical order is HND
+                cache = flat.view(nb_d, H, Nd, D).permute(0, 2, 1, 3)
+                kv_postprocess_blksize_on_receive(cache, idx, ratio)
+            else:
+                cache = flat.view(nb_d, Nd, H, D)
+                kv_postprocess_blksize_and_layout_on_receive(cache, idx, ratio)
+        out[name] = d
+    np.savez_compressed(os.path.join(HERE, "blocksize_ratio.npz"), p_pool=p, p_table=p_table, d_table=d_table,
+                        d_expect_hnd=out["hnd"], d_expect_nhd=out["nhd"],
+                        shape=np.array([L, H, D, Np, ratio, nb_p, nb_d, n_p], dtype=np.int64))
+    print("blocksize_ratio.npz written")
+
+
 def tp_fixture():
     from vllm.distributed.kv_transfer.kv_connector.utils import TransferTopology
     from vllm.distributed.kv_transfer.kv_connector.v1.nixl.tp_mapping import compute_tp_mapping
@@ -57,7 +96,9 @@ def tp_fixture():
     import inspect
 
     rows = []
-    cases = [(2, 4, 8), (4, 2, 8), (2, 1, 8), (1, 4, 8), (1, 1, 8), (8, 2, 8), (4, 4, 8), (1, 2, 8), (8, 8, 8), (2, 8, 8)]
+    cases = [(2, 4, 8), (4, 2, 8), (2, 1, 8), (1, 4, 8), (1, 1, 8), (8, 2, 8), (4, 4, 8), (1, 2, 8), (8, 8, 8), (2, 8, 8),
+             # tp > kv heads: KV is replicated across ranks (kv_connector/utils.py:525-538)
+             (16, 8, 8), (8, 16, 8), (16, 16, 8), (4, 16, 8), (16, 4, 8), (4, 8, 2), (8, 4, 2)]
     sig = inspect.signature(TransferTopology)
     for d_tp, p_tp, heads in cases:
         for d_rank in range(d_tp):
@@ -93,4 +134,5 @@ def tp_fixture():
 
 if __name__ == "__main__":
     layout_fixture()
+    blocksize_fixture()
     tp_fixture()

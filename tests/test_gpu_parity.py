@@ -125,6 +125,80 @@ def test_tp_reshard_staged(ctx):
     assert np.array_equal(ddev.bytes(), dpool.buf)
 
 
+REGROUP = [
+    # Ns, Nd, src layout, dst layout, H_src, H_dst, (src_off, dst_off, heads), granules
+    (16, 64, o.HND, o.HND, 8, 8, None, 23),
+    (16, 32, o.HND, o.NHD, 8, 8, None, 16),
+    (16, 64, o.NHD, o.NHD, 8, 8, None, 9),
+    (16, 32, o.NHD, o.HND, 8, 8, None, 31),
+    (64, 16, o.HND, o.NHD, 8, 8, None, 20),     # big prefill blocks into small decode blocks
+    (32, 16, o.NHD, o.HND, 4, 4, None, 7),
+    (16, 64, o.HND, o.NHD, 2, 4, (0, 2, 2), 12),  # regroup + TP slot in one pass
+    (16, 32, o.NHD, o.HND, 4, 2, (2, 0, 2), 10),
+]
+
+
+@pytest.mark.parametrize("case", REGROUP, ids=lambda c: f"N{c[0]}to{c[1]}-{c[2]}{c[3]}-H{c[4]}to{c[5]}-n{c[7]}")
+def test_block_size_regroup_matches_oracle(cfg_ctx, case):
+    Ns, Nd, ls, ld, Hs, Hd, sl, n = case
+    N = min(Ns, Nd)
+    ks, kd = Ns // N, Nd // N
+    ns, nd = -(-n // ks), -(-n // kd)
+    src = o.make_pool(2, Hs, 128, ns + 5, ls, block_tokens=Ns, seed=61)
+    dst = o.make_pool(2, Hd, 128, nd + 6, ld, block_tokens=Nd, fill="canary")
+    ts, td = o.make_table(ns + 5, ns, 1), o.make_table(nd + 6, nd, 2)
+    xf_o = o.Xform(*sl) if sl else None
+    xf_k = kvx.Xform(sl[0], sl[1], sl[2], ld) if sl else None
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n, xf_k)
+    torch.cuda.synchronize()
+    o.handoff_regroup(src, ts, dst, td, xf_o, n_small=n)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    # the host-table entry uploads ceil(n/k) ids per side
+    ddst2 = DevPool(cfg_ctx, o.make_pool(2, Hd, 128, nd + 6, ld, block_tokens=Nd, fill="canary"))
+    cfg_ctx.handoff_host(dsrc.kp, ts, ddst2.kp, td, n, xf_k)
+    torch.cuda.synchronize()
+    assert np.array_equal(ddst2.bytes(), dst.buf)
+
+
+def test_golden_blocksize_fixture_on_gpu(cfg_ctx, golden_dir):
+    """vLLM's kv_postprocess_blksize[_and_layout]_on_receive outputs, reproduced in flight."""
+    from test_oracle import _pool_from_regions
+
+    g = np.load(os.path.join(golden_dir, "blocksize_ratio.npz"))
+    L, H, D, Np, ratio, nb_p, nb_d, n_p = [int(x) for x in g["shape"]]
+    src = _pool_from_regions(g["p_pool"], o.HND, H, D, Np)
+    for name, lay in (("hnd", o.HND), ("nhd", o.NHD)):
+        dst = _pool_from_regions(np.full((2 * L, nb_d, Np * ratio * H * D), o.CANARY16, dtype=np.uint16), lay, H, D, Np * ratio)
+        dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+        cfg_ctx.handoff_fused(dsrc.kp, dev_table(g["p_table"]), ddst.kp, dev_table(g["d_table"]), n_p)
+        torch.cuda.synchronize()
+        assert np.array_equal(ddst.bytes(), np.ascontiguousarray(g["d_expect_" + name]).view(np.uint8).reshape(-1))
+
+
+ODD = [
+    # L, H, D, E, src layout, dst layout, n   — fp8 KV (E=1) and row sizes that are not powers of two
+    (2, 8, 128, 1, o.HND, o.NHD, 21),
+    (2, 8, 64, 1, o.NHD, o.HND, 9),
+    (1, 4, 96, 2, o.HND, o.NHD, 14),
+    (1, 5, 80, 2, o.NHD, o.HND, 6),
+    (1, 40, 128, 2, o.HND, o.NHD, 3),   # a 160 KiB chunk: head unit 4 KiB, 10 pieces per chunk
+]
+
+
+@pytest.mark.parametrize("case", ODD, ids=lambda c: f"H{c[1]}D{c[2]}E{c[3]}-{c[4]}{c[5]}")
+def test_other_element_and_row_sizes(cfg_ctx, case):
+    L, H, D, E, ls, ld, n = case
+    src = o.make_pool(L, H, D, n + 3, ls, elem_bytes=E, seed=5)
+    dst = o.make_pool(L, H, D, n + 4, ld, elem_bytes=E, fill="canary")
+    ts, td = o.make_table(n + 3, n, 1), o.make_table(n + 4, n, 2)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n)
+    torch.cuda.synchronize()
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+
+
 def test_golden_fixture_on_gpu(cfg_ctx, golden_dir):
     g = np.load(os.path.join(golden_dir, "layout_hnd_to_nhd.npz"))
     L, H, N, D, nb_p, nb_d, n = [int(x) for x in g["shape"]]

@@ -35,6 +35,48 @@ def test_golden_layout_hnd_to_nhd(golden_dir):
     assert np.array_equal(dst2.buf, want)
 
 
+def test_golden_blocksize_ratio(golden_dir):
+    """Oracle regroup (4-token P blocks → 16-token D blocks) == raw landing + vLLM's
+    kv_postprocess_blksize_on_receive (HND kept) / kv_postprocess_blksize_and_layout_on_receive (→ NHD)."""
+    g = np.load(os.path.join(golden_dir, "blocksize_ratio.npz"))
+    L, H, D, Np, ratio, nb_p, nb_d, n_p = [int(x) for x in g["shape"]]
+    src = _pool_from_regions(g["p_pool"], o.HND, H, D, Np)
+    for name, lay in (("hnd", o.HND), ("nhd", o.NHD)):
+        want = np.ascontiguousarray(g["d_expect_" + name]).view(np.uint8).reshape(-1)
+        for impl in ("numpy", "c"):
+            dst = _pool_from_regions(np.full((2 * L, nb_d, Np * ratio * H * D), o.CANARY16, dtype=np.uint16), lay, H, D, Np * ratio)
+            if impl == "numpy":
+                o.handoff(src, g["p_table"], dst, g["d_table"])
+            else:
+                assert oc.handoff(src, g["p_table"], dst, g["d_table"], threads=2) == 0
+            assert np.array_equal(dst.buf, want), (name, impl)
+
+
+@pytest.mark.parametrize("Ns,Nd", [(16, 64), (64, 16), (16, 32), (32, 16)])
+@pytest.mark.parametrize("layouts", [(o.HND, o.HND), (o.HND, o.NHD), (o.NHD, o.NHD), (o.NHD, o.HND)])
+def test_regroup_numpy_vs_c_and_round_trip(Ns, Nd, layouts):
+    ls, ld = layouts
+    N = min(Ns, Nd)
+    n = 2 * (max(Ns, Nd) // N) + 1  # a partially filled last big block
+    ns, nd = -(-n // (Ns // N)), -(-n // (Nd // N))
+    src = o.make_pool(1, 4, 32, ns + 2, ls, block_tokens=Ns, seed=8)
+    d1 = o.make_pool(1, 4, 32, nd + 3, ld, block_tokens=Nd, fill="canary")
+    d2 = o.make_pool(1, 4, 32, nd + 3, ld, block_tokens=Nd, fill="canary")
+    ts, td = o.make_table(ns + 2, ns, 1), o.make_table(nd + 3, nd, 2)
+    o.handoff_regroup(src, ts, d1, td, n_small=n)
+    s, d = oc._paged(src, ts, 0, keep := []), oc._paged(d2, td, 0, keep)
+    import ctypes
+    assert oc.lib().kvxo_xfer(ctypes.byref(s), ctypes.byref(d), 2, n, N, 4, 64, 2) == 0
+    assert np.array_equal(d1.buf, d2.buf)
+    # and back again into a fresh source-shaped pool: the moved granules are restored bit for bit
+    back = o.make_pool(1, 4, 32, ns + 2, ls, block_tokens=Ns, fill="canary")
+    o.handoff_regroup(d1, td, back, ts, n_small=n)
+    for r in range(2):
+        a = o._rows(src.region_view(r)[ts], ls, Ns, 4, 64).reshape(-1, 4, 64)[: n * N]
+        b = o._rows(back.region_view(r)[ts], ls, Ns, 4, 64).reshape(-1, 4, 64)[: n * N]
+        assert np.array_equal(a, b)
+
+
 def test_golden_tp_mapping(golden_dir):
     rows = json.load(open(os.path.join(golden_dir, "tp_mapping.json")))["rows"]
     assert len(rows) >= 30
