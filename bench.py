@@ -337,6 +337,7 @@ def run_single(args):
     stage = torch.empty(payload, dtype=torch.uint8, device="cuda")
     stage2 = torch.empty(payload, dtype=torch.uint8, device="cuda")
     xf = kvx.Xform(0, 0, 0, kvx.NHD)
+    asc = [torch.arange(1 + j * n, 1 + (j + 1) * n, dtype=torch.int32, device="cuda") for j in range(sets)]
     parts = {}
     reps = max(3, min(args.steps, 10))
     for name, fn in (
@@ -344,6 +345,8 @@ def run_single(args):
         ("copy_local", lambda k: ctx.copy(stage, stage2, payload, None, 0, stream)),
         ("scatter_nhd", lambda k: ctx.scatter(stage2, D.pool, d_dst[k % sets], n, xf, stream)),
         ("fused_identity_hnd", lambda k: ctx.handoff_fused(P.pool, d_src[k % sets], P.pool, d_dst[(k + 1) % sets], n, None, None, 0, stream)),
+        # best-case control: contiguous ascending block ids on both sides
+        ("fused_hnd_to_nhd_contiguous_tables", lambda k: ctx.handoff_fused(P.pool, asc[k % sets], D.pool, asc[(k + 1) % sets], n, None, None, 0, stream)),
     ):
         for k in range(3):
             fn(k)

@@ -196,6 +196,7 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   uint64_t* flag = nullptr;
   uint64_t flag_val = 0;
   bool copy_mode = false;  // contiguous→contiguous bytes (kvx_copy)
+  bool dst_is_peer = true;  // unknown destinations are treated as remote
   uint64_t copy_bytes = 0;
 };
 
@@ -287,6 +288,10 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.stages = stages; p.stage_bytes = stage_bytes;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
   p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
+  // Device-scope fences are enough when nobody outside this GPU observes the flag: the flag is one of
+  // this context's own slots and the destination pool was not imported from a peer.
+  p.flag_local = (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags && !ls.dst_is_peer &&
+                  env_or("KVX_FORCE_SYS_FENCE", 0) == 0) ? 1u : 0u;
   p.flag_val = ls.flag_val;
   p.status = ctx->d_status;
   p.done_counter = ctx->d_counters + (ctx->counter_cursor++ % kNumCounters);
@@ -889,6 +894,7 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
   ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
   ls.flag = flag;
   ls.flag_val = flag_val;
+  ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
   return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
 }
 

@@ -52,6 +52,7 @@ struct XferParams {
   unsigned int d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b;
   unsigned int stages, stage_bytes;
   unsigned int l2_hint;
+  unsigned int flag_local;   // 1: flag and destination live on this GPU → device-scope fences suffice
   unsigned long long* flag;  // completion flag (local or peer memory) or null
   unsigned long long flag_val;
   unsigned int* done_counter;  // scratch: CTAs finished (zero on entry, zero again on exit)
@@ -232,10 +233,10 @@ __device__ __forceinline__ void finish_and_flag(const XferParams& p) {
   // (the pattern cooperative-groups grid sync uses): one fence per CTA instead of one per thread.
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
+    if (p.flag_local) __threadfence(); else __threadfence_system();
     const unsigned prev = atomicAdd(p.done_counter, 1u);
     if (prev == gridDim.x - 1) {
-      __threadfence_system();
+      if (p.flag_local) __threadfence(); else __threadfence_system();
       *p.done_counter = 0u;
       asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
     }
