@@ -1,0 +1,113 @@
+"""OpenAI-compatible Frontend stand-in: the HTTP contract chat.sh / multi_convos_parallel.sh / aiperf rely on,
+and the metric names the reference's Grafana dashboard queries."""
+import json
+import urllib.error
+import urllib.request
+
+import pytest
+
+from kvx.frontend import Frontend, count_tokens
+
+
+class FakeBackend:
+    """Host-logic double: the HTTP layer is tested on CPU; the GPU test below uses the real workers."""
+
+    def __init__(self):
+        self.calls = []
+
+    def handoff(self, isl):
+        self.calls.append(isl)
+        if isl > 100000:
+            raise RuntimeError("boom")
+        return 0.001, isl * 1000, 56 * isl
+
+
+def _post(url, body):
+    req = urllib.request.Request(url, json.dumps(body).encode(), {"Content-Type": "application/json", "Authorization": "Bearer dummy"})
+    try:
+        with urllib.request.urlopen(req) as r:
+            return r.status, json.loads(r.read())
+    except urllib.error.HTTPError as e:
+        return e.code, json.loads(e.read())
+
+
+@pytest.fixture()
+def server():
+    be = FakeBackend()
+    fe = Frontend("Qwen/Qwen3-0.6B", be)
+    srv = fe.serve("127.0.0.1", 0)
+    yield f"http://127.0.0.1:{srv.server_address[1]}", be
+    srv.shutdown()
+
+
+def test_chat_completion_contract(server):
+    base, be = server
+    msgs = [{"role": "system", "content": "You are terse."}, {"role": "user", "content": "hello " * 200}]
+    code, resp = _post(base + "/v1/chat/completions", {"model": "Qwen/Qwen3-0.6B", "messages": msgs, "temperature": 0, "max_tokens": 512})
+    assert code == 200 and "error" not in resp
+    assert resp["choices"][0]["message"]["role"] == "assistant" and resp["choices"][0]["message"]["content"]
+    assert resp["usage"]["prompt_tokens"] == count_tokens(msgs) == be.calls[0]
+    assert resp["kv_transfer"]["bytes_transferred"] == be.calls[0] * 1000
+    with urllib.request.urlopen(base + "/v1/models") as r:
+        assert json.loads(r.read())["data"][0]["id"] == "Qwen/Qwen3-0.6B"
+
+
+def test_errors_are_json_error_objects(server):
+    base, _ = server
+    code, resp = _post(base + "/v1/chat/completions", {"model": "other", "messages": [{"role": "user", "content": "x"}]})
+    assert code == 404 and "message" in resp["error"]
+    code, resp = _post(base + "/v1/chat/completions", {"model": "Qwen/Qwen3-0.6B", "messages": []})
+    assert code == 400 and "error" in resp
+    code, resp = _post(base + "/v1/chat/completions", {"model": "Qwen/Qwen3-0.6B", "messages": [{"role": "user", "content": "y" * 500000}]})
+    assert code == 500 and "KV handoff failed" in resp["error"]["message"]
+
+
+def test_dashboard_metric_names(server):
+    base, _ = server
+    for _ in range(3):
+        _post(base + "/v1/chat/completions", {"model": "Qwen/Qwen3-0.6B", "messages": [{"role": "user", "content": "hi there"}]})
+    with urllib.request.urlopen(base + "/metrics") as r:
+        text = r.read().decode()
+    for name in ("dynamo_frontend_requests_total", "dynamo_frontend_time_to_first_token_seconds_sum",
+                 "dynamo_frontend_time_to_first_token_seconds_count", "dynamo_frontend_inter_token_latency_seconds_sum",
+                 "dynamo_frontend_request_duration_seconds_count", "dynamo_frontend_input_sequence_tokens_sum",
+                 "dynamo_frontend_output_sequence_tokens_count", "vllm:nixl_xfer_time_seconds_sum",
+                 "vllm:nixl_bytes_transferred_sum", "vllm:nixl_num_descriptors_count"):
+        assert name in text, name
+    assert 'dynamo_frontend_requests_total{model="Qwen/Qwen3-0.6B",namespace="default",status="success"} 3.0' in text
+
+
+def test_streaming_is_sse(server):
+    base, _ = server
+    req = urllib.request.Request(base + "/v1/chat/completions", json.dumps(
+        {"model": "Qwen/Qwen3-0.6B", "messages": [{"role": "user", "content": "hi"}], "stream": True}).encode(),
+        {"Content-Type": "application/json"})
+    with urllib.request.urlopen(req) as r:
+        body = r.read().decode()
+        assert r.headers["Content-Type"] == "text/event-stream"
+    assert body.startswith("data: {") and body.rstrip().endswith("data: [DONE]")
+
+
+@pytest.mark.gpu
+def test_frontend_runs_real_handoffs():
+    """Three conversations' worth of requests through the real prefill/decode workers."""
+    import kvx
+    from kvx.frontend import InProcessHandoff
+
+    be = InProcessHandoff(kvx.KV_SHAPES["meta-llama/Llama-3.2-1B-Instruct"], max_isl=4096)
+    fe = Frontend("meta-llama/Llama-3.2-1B-Instruct", be)
+    srv = fe.serve("127.0.0.1", 0)
+    base = f"http://127.0.0.1:{srv.server_address[1]}"
+    try:
+        for words in (40, 900, 3000):
+            code, resp = _post(base + "/v1/chat/completions", {"model": "meta-llama/Llama-3.2-1B-Instruct",
+                                                                "messages": [{"role": "user", "content": "token " * words}], "max_tokens": 8})
+            assert code == 200, resp
+            kv = resp["kv_transfer"]
+            n = -(-resp["usage"]["prompt_tokens"] // 16)
+            assert kv["bytes_transferred"] == n * 32 * 16384 and kv["num_descriptors"] == n * 32 and kv["xfer_time_seconds"] > 0
+        # blocks were freed on both sides after every request
+        assert be.p.blocks.free_blocks == be.d.blocks.free_blocks == 3 * 256
+    finally:
+        srv.shutdown()
+        be.close()
