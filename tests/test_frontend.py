@@ -104,7 +104,7 @@ def test_frontend_runs_real_handoffs():
                                                                 "messages": [{"role": "user", "content": "token " * words}], "max_tokens": 8})
             assert code == 200, resp
             kv = resp["kv_transfer"]
-            n = -(-resp["usage"]["prompt_tokens"] // 16)
+            n = min(256, -(-resp["usage"]["prompt_tokens"] // 16))  # prompts are clipped to max_isl
             assert kv["bytes_transferred"] == n * 32 * 16384 and kv["num_descriptors"] == n * 32 and kv["xfer_time_seconds"] > 0
         # blocks were freed on both sides after every request
         assert be.p.blocks.free_blocks == be.d.blocks.free_blocks == 3 * 256
