@@ -70,6 +70,7 @@ struct kvx_ctx {
   cudaStream_t aux = nullptr;
   std::string last_error;
   std::map<void*, std::string> imported;  // imported pointer → handle key ("" = same process)
+  std::map<const void*, size_t> smem_limit;  // kernel → dynamic shared memory limit already set
 };
 
 struct kvx_pool {
@@ -208,9 +209,14 @@ bool all_aligned(uint64_t a, const Plan& pl, const XferSide& s, const XferSide& 
          m(s.block_stride) && m(d.block_stride) && m(s.base0) && m(d.base0);
 }
 
+// Raise a kernel's dynamic shared-memory limit once per (context, kernel): later launches — including
+// ones issued while a stream is being captured into a CUDA graph — make no attribute call.
 template <typename K>
 int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
+  size_t& have = ctx->smem_limit[reinterpret_cast<const void*>(kernel)];
+  if (have >= bytes) return KVX_OK;
   KVX_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
+  have = bytes;
   return KVX_OK;
 }
 

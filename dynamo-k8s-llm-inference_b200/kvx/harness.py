@@ -36,6 +36,8 @@ class StreamConfig:
     concurrency: int = 1
     verify: bool = True
     decode_layout: Optional[int] = None  # None = manifest's
+    route: str = "pair"  # "pair": decode replica i reads prefill replica i % nP; "spread": request q of decode
+    #                       replica i reads prefill replica (i + q) % nP (with concurrency >= nP this is an incast)
     options: Dict[str, int] = field(default_factory=dict)  # kvx context options
 
 
@@ -126,9 +128,9 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
     metas = [None] * world
     dist.all_gather_object(metas, w.metadata())
 
-    # which prefill replica feeds decode replica i: round-robin over the prefill replicas
-    def src_replica(d_rep: int) -> int:
-        return d_rep % n_p_rep
+    # which prefill replica feeds request q of decode replica i
+    def src_replica(d_rep: int, q: int = 0) -> int:
+        return (d_rep + q) % n_p_rep if cfg.route == "spread" else d_rep % n_p_rep
 
     def p_rank_of(rep: int, t: int) -> int:
         return next(p.rank for p in p_ranks if p.replica == rep and p.tp_rank == t)
@@ -136,7 +138,8 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
     result = None
     if me.role == "prefill":
         # block ids of every request of every stream this replica serves (same on all its TP ranks)
-        served = [d for d in d_ranks if d.tp_rank == 0 and src_replica(d.replica) == me.replica]
+        served = [d for d in d_ranks if d.tp_rank == 0 and
+                  any(src_replica(d.replica, q) == me.replica for q in range(len(counts)))]
         ids = {d.replica: _pre_allocate(nb, counts, SEED + 7 + 100 * me.replica + d.replica, hold) for d in served}
         box = [ids]
     else:
@@ -146,9 +149,11 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
 
     if me.role == "decode":
         srcs = [e for e in edges if e.d_rank == me.tp_rank]
-        for e in srcs:
-            w.add_remote(e.p_rank, metas[p_rank_of(src_replica(me.replica), e.p_rank)])
-        remote_ids = all_ids[p_rank_of(src_replica(me.replica), 0)][me.replica]
+        p_reps = sorted({src_replica(me.replica, q) for q in range(len(counts))})
+        for pr in p_reps:
+            for e in srcs:
+                w.add_remote(pr * 1000 + e.p_rank, metas[p_rank_of(pr, e.p_rank)])
+        remote_ids = [all_ids[p_rank_of(src_replica(me.replica, q), 0)][me.replica][q] for q in range(len(counts))]
         local_ids = _pre_allocate(nb, counts, SEED + 13 + 100 * me.replica, hold)  # same on all TP ranks of a replica
         c = max(1, cfg.concurrency)
         streams = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
@@ -169,7 +174,7 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
                 if j:
                     lane[j].wait_event(ev[q][0])
                 # release slot: one flag per (request, consumer TP rank) in the prefill rank's memory
-                w.pull(e.p_rank, remote_ids[q], local_ids[q], notify_slot=(q * d_tp + me.tp_rank) % w.num_flags,  # flag slot in the prefill rank's memory
+                w.pull(src_replica(me.replica, q) * 1000 + e.p_rank, remote_ids[q], local_ids[q], notify_slot=(q * d_tp + me.tp_rank) % w.num_flags,  # flag slot in the prefill rank's memory
                        value=q + 1, edge=e if (p_tp != d_tp) else None, host_tables=True, stream=lane[j])
             for j in range(1, len(srcs)):
                 done_j = torch.cuda.Event()
@@ -191,7 +196,7 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
                             "time_to_first_token_added_ms": 1e3 * (t_done[q] - t_sub[q])})
         ok = True
         if cfg.verify:
-            ok = _verify_tail(torch, w, shape, srcs, p_tp, d_tp, src_replica(me.replica), remote_ids, local_ids, counts, nb,
+            ok = _verify_tail(torch, w, shape, srcs, p_tp, d_tp, src_replica(me.replica, len(counts) - 1), remote_ids, local_ids, counts, nb,
                               me, HND, NHD)
         total_b = sum(r["bytes_transferred"] for r in per_req)
         result = {"rank": rank, "role": "decode", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
@@ -201,14 +206,18 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
         dist.barrier()
         # the producer side only learns of completion through release flags written by the consumers
         consumers = d_tp // p_tp if d_tp > p_tp else 1
-        served_d = sorted(ids)
         deadline = time.time() + 120
-        last = len(counts) - 1
-        pending = {(dr, t) for dr in served_d for t in range(d_tp) if any(e.p_rank == me.tp_rank and e.d_rank == t for e in edges)}
+        pending = set()
+        for dr in sorted(ids):  # the last request of every stream that routes to this replica
+            mine = [q for q in range(len(counts)) if src_replica(dr, q) == me.replica]
+            if mine:
+                for t in range(d_tp):
+                    if any(e.p_rank == me.tp_rank and e.d_rank == t for e in edges):
+                        pending.add((mine[-1], t))
         while pending and time.time() < deadline:
             for key in list(pending):
-                _, t = key
-                if w.poll((last * d_tp + t) % w.num_flags, last + 1):
+                q_last, t = key
+                if w.poll((q_last * d_tp + t) % w.num_flags, q_last + 1):
                     pending.discard(key)
             time.sleep(0.002)
         result = {"rank": rank, "role": "prefill", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,

@@ -331,3 +331,57 @@ def test_full_size_properties_qwen3_32k(cfg):
     for dp in (P, Dp, P2):
         dp.free()
     c.close()
+
+
+def test_layerwise_handoff_equals_whole(ctx):
+    """Layer-wise transfer (overlap with the tail of prefill): one registered pool per layer group, one
+    handoff per group as its KV becomes ready, equals the whole-request handoff."""
+    L, H, D, n = 6, 8, 128, 25
+    src = o.make_pool(L, H, D, n + 4, o.HND, seed=17)
+    whole = o.make_pool(L, H, D, n + 5, o.NHD, fill="canary")
+    ts, td = o.make_table(n + 4, n, 1), o.make_table(n + 5, n, 2)
+    o.handoff(src, ts, whole, td)
+    t_src = torch.from_numpy(src.buf.copy()).cuda()
+    t_dst = torch.from_numpy(o.make_pool(L, H, D, n + 5, o.NHD, fill="canary").buf).cuda()
+    streams = [torch.cuda.Stream() for _ in range(3)]
+    dts, dtd = dev_table(ts), dev_table(td)
+    torch.cuda.synchronize()
+    pools = []
+    for g in range(3):  # three groups of two layers (= four regions) each
+        regs = range(4 * g, 4 * g + 4)
+        ps = ctx.register_pool([t_src.data_ptr() + src.region_off[r] for r in regs], num_blocks=n + 4, heads=H, head_dim=D, layout=kvx.HND)
+        pd = ctx.register_pool([t_dst.data_ptr() + whole.region_off[r] for r in regs], num_blocks=n + 5, heads=H, head_dim=D, layout=kvx.NHD)
+        pools += [ps, pd]
+        ctx.handoff_fused(ps, dts, pd, dtd, n, stream=streams[g])
+    torch.cuda.synchronize()
+    assert np.array_equal(t_dst.cpu().numpy(), whole.buf)
+    for p in pools:
+        p.release()
+
+
+def test_cuda_graph_capture_and_replay(ctx):
+    """The device-table entry makes no allocation and no synchronisation: it can be captured in a CUDA
+    graph and replayed with new table CONTENTS (same buffers), as a decode loop would."""
+    L, H, D, n = 2, 8, 128, 40
+    src = o.make_pool(L, H, D, 3 * n, o.HND, seed=23)
+    dst = o.make_pool(L, H, D, 3 * n, o.NHD, fill="canary")
+    dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
+    ts, td = dev_table(o.make_table(3 * n, n, 1)), dev_table(o.make_table(3 * n, n, 2))
+    flags, _ = ctx.flags()
+    ctx.flag_reset(flags + 8 * 9, 0)
+    ctx.handoff_fused(dsrc.kp, ts, ddst.kp, td, n, flag=flags + 8 * 9, flag_val=1)  # warm-up outside capture
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.graph(g, stream=s):
+        ctx.handoff_fused(dsrc.kp, ts, ddst.kp, td, n, flag=flags + 8 * 9, flag_val=2, stream=s)
+    o.handoff(src, ts.cpu().numpy(), dst, td.cpu().numpy())
+    for rep in range(2):  # replay with fresh tables written into the same device buffers
+        t1, t2 = o.make_table(3 * n, n, 10 + rep), o.make_table(3 * n, n, 20 + rep)
+        ts.copy_(torch.from_numpy(t1)); td.copy_(torch.from_numpy(t2))
+        g.replay()
+        torch.cuda.synchronize()
+        o.handoff(src, t1, dst, t2)
+        assert np.array_equal(ddst.bytes(), dst.buf)
+        assert ctx.flag_poll(flags + 8 * 9, 2)
+    ctx.check()
