@@ -186,35 +186,61 @@ __device__ __forceinline__ void lds_vec(Vec<32>& r, const unsigned char* s) {
 // ----------------------------------------------------------------------------------------------
 // Item decode: item w → (piece, i, region) → source / destination byte address.  A block id outside
 // [0, num_blocks) yields bytes == 0 (the item is skipped) and raises kStatusBadBlockId.
+// The decode is split in two so that the producer can have the NEXT batch's table and base loads in
+// flight while it issues the current batch: item_load only issues loads (all four back to back, no
+// branch between them), item_finish consumes them.
 // ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned long long side_addr(const XferSide& s, unsigned r, unsigned i, unsigned piece,
-                                                        unsigned n, bool& ok) {
+struct RawSide {
+  unsigned long long base;
+  int id;
+};
+struct RawItem {
+  RawSide s, d;
+  unsigned w, r, i, piece;
+};
+
+__device__ __forceinline__ void side_load(const XferSide& s, unsigned r, unsigned i, RawSide& out) {
+  out.id = 0;
+  out.base = 0;
+  if (s.bases != nullptr) {
+    const unsigned blk = i / s.ratio;
+    out.id = s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
+    out.base = __ldg(s.bases + r);
+  }
+}
+
+__device__ __forceinline__ unsigned long long side_finish(const XferSide& s, const RawSide& raw, unsigned r, unsigned i,
+                                                          unsigned piece, unsigned n, bool& ok) {
   unsigned long long a;
   if (s.bases != nullptr) {
-    const unsigned blk = i / s.ratio, sub = i % s.ratio;
-    const int id = s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
-    if (id < 0 || static_cast<unsigned long long>(id) >= s.num_blocks) {
+    if (raw.id < 0 || static_cast<unsigned long long>(raw.id) >= s.num_blocks) {
       ok = false;
       return 0;
     }
-    a = __ldg(s.bases + r) + static_cast<unsigned long long>(id) * s.block_stride +
-        static_cast<unsigned long long>(sub) * s.sub_stride;
+    a = raw.base + static_cast<unsigned long long>(raw.id) * s.block_stride +
+        static_cast<unsigned long long>(i % s.ratio) * s.sub_stride;
   } else {
     a = s.base0 + (static_cast<unsigned long long>(r) * n + i) * s.block_stride;
   }
   return a + s.slice_off + static_cast<unsigned long long>(piece) * s.piece_stride;
 }
 
-__device__ __forceinline__ void decode_item(const XferParams& p, unsigned w, unsigned long long& sa,
-                                            unsigned long long& da, unsigned& bytes) {
-  const unsigned piece = w % p.ppc;
+__device__ __forceinline__ void item_load(const XferParams& p, unsigned w, RawItem& raw) {
+  raw.w = w;
+  raw.piece = w % p.ppc;
   const unsigned c = w / p.ppc;
-  const unsigned i = c % p.n;
-  const unsigned r = c / p.n;
+  raw.i = c % p.n;
+  raw.r = c / p.n;
+  side_load(p.src, raw.r, raw.i, raw.s);
+  side_load(p.dst, raw.r, raw.i, raw.d);
+}
+
+__device__ __forceinline__ void item_finish(const XferParams& p, const RawItem& raw, unsigned long long& sa,
+                                            unsigned long long& da, unsigned& bytes) {
   bool ok = true;
-  sa = side_addr(p.src, r, i, piece, p.n, ok);
-  da = side_addr(p.dst, r, i, piece, p.n, ok);
-  bytes = (p.tail_bytes != 0 && w == p.total_items - 1) ? p.tail_bytes : p.piece_bytes;
+  sa = side_finish(p.src, raw.s, raw.r, raw.i, raw.piece, p.n, ok);
+  da = side_finish(p.dst, raw.d, raw.r, raw.i, raw.piece, p.n, ok);
+  bytes = (p.tail_bytes != 0 && raw.w == p.total_items - 1) ? p.tail_bytes : p.piece_bytes;
   if (!ok) {
     bytes = 0;
     atomicOr(p.status, kStatusBadBlockId);
@@ -277,10 +303,14 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
   if (warp == 0) {
     // ------------------------------ producer ------------------------------
     const unsigned long long pol = p.l2_hint ? l2_policy_evict_first() : 0ull;
+    RawItem raw{};
+    if (lane < my_items) item_load(p, bid + lane * grid, raw);
     for (unsigned base = 0; base < my_items; base += 32u) {
       unsigned long long sa = 0, da = 0;
       unsigned bytes = 0;
-      if (base + lane < my_items) decode_item(p, bid + (base + lane) * grid, sa, da, bytes);
+      if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
+      // next batch's lookups travel while this batch is issued
+      if (base + 32u + lane < my_items) item_load(p, bid + (base + 32u + lane) * grid, raw);
       const unsigned cnt = min(32u, my_items - base);
       for (unsigned j = 0; j < cnt; ++j) {
         const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
@@ -407,10 +437,13 @@ __global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
   const unsigned bid = blockIdx.x;
   const unsigned grid = gridDim.x;
   const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+  RawItem raw{};
+  if (lane < my_items) item_load(p, bid + lane * grid, raw);
   for (unsigned base = 0; base < my_items; base += 32u) {
     unsigned long long sa = 0, da = 0;
     unsigned bytes = 0;
-    if (base + lane < my_items) decode_item(p, bid + (base + lane) * grid, sa, da, bytes);
+    if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
+    if (base + 32u + lane < my_items) item_load(p, bid + (base + 32u + lane) * grid, raw);
     const unsigned cnt = min(32u, my_items - base);
     for (unsigned j = 0; j < cnt; ++j) {
       const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);

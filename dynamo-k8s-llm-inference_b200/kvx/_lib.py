@@ -6,7 +6,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libkvx.so")
+# KVX_LIB_PATH points at another build of the same library (A/B runs of kernel variants under tools/).
+LIB_PATH = os.environ.get("KVX_LIB_PATH") or os.path.join(os.path.dirname(_HERE), "lib", "libkvx.so")
 
 c_i32, c_u32, c_i64, c_u64 = ctypes.c_int32, ctypes.c_uint32, ctypes.c_int64, ctypes.c_uint64
 c_vp, c_sz = ctypes.c_void_p, ctypes.c_size_t
