@@ -220,6 +220,25 @@ int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
   return KVX_OK;
 }
 
+// One launch.  With `pdl` the kernel is allowed to become resident while the previous kernel on the
+// stream is still draining (programmatic dependent launch); the kernels wait for that kernel's
+// completion themselves before they touch global memory (grid_dep_wait in kvx_kernels.cuh).
+template <typename K>
+cudaError_t launch_kernel(K kernel, uint32_t grid, uint32_t block, size_t smem, cudaStream_t stream, bool pdl,
+                          const XferParams& p) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1u : 0u;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>* src_bases,
                     const std::vector<void*>* dst_bases, cudaStream_t stream) {
   DeviceGuard guard(ctx->device);
@@ -232,6 +251,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   const uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
   const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
   int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);
+  const bool pdl = ctx->opt[KVX_OPT_PDL] != 0;
   if (engine == kEngineAuto) engine = kEngineTma;
 
   constexpr uint32_t kLdgThreads = 256;
@@ -325,28 +345,28 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
       auto k = kvx::kvx_xfer_tma_kernel<0, 1>;
       int32_t rc = set_smem(ctx, k, smem);
       if (rc) return rc;
-      k<<<grid, 32u * (1u + cons_warps), smem, stream>>>(p);
+      KVX_CUDA(ctx, launch_kernel(k, grid, 32u * (1u + cons_warps), smem, stream, pdl, p));
     } else {
       const uint32_t T = cons_warps * 32u;
       if (vec_opt == 32 && static_cast<uint64_t>(T) * 4u * 32u >= pl.piece_bytes) {
         auto k = kvx::kvx_xfer_tma_kernel<32, 4>;
         int32_t rc = set_smem(ctx, k, smem);
         if (rc) return rc;
-        k<<<grid, 32u + T, smem, stream>>>(p);
+        KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
       } else if (static_cast<uint64_t>(T) * 8u * 16u >= pl.piece_bytes) {
         auto k = kvx::kvx_xfer_tma_kernel<16, 8>;
         int32_t rc = set_smem(ctx, k, smem);
         if (rc) return rc;
-        k<<<grid, 32u + T, smem, stream>>>(p);
+        KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
       } else {
         return KVX_EINVAL;  // stage larger than the consumer threads can drain: raise CONSUMER_WARPS
       }
     }
   } else {
     if (vec_opt == 32 && pl.piece_bytes <= ldg_cap32) {
-      kvx::kvx_xfer_ldg_kernel<32, 4><<<grid, kLdgThreads, 0, stream>>>(p);
+      KVX_CUDA(ctx, launch_kernel(kvx::kvx_xfer_ldg_kernel<32, 4>, grid, kLdgThreads, 0, stream, pdl, p));
     } else {
-      kvx::kvx_xfer_ldg_kernel<16, 8><<<grid, kLdgThreads, 0, stream>>>(p);
+      KVX_CUDA(ctx, launch_kernel(kvx::kvx_xfer_ldg_kernel<16, 8>, grid, kLdgThreads, 0, stream, pdl, p));
     }
   }
   KVX_CUDA(ctx, cudaGetLastError());
@@ -554,6 +574,7 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->opt[KVX_OPT_VEC_BYTES] = env_or("KVX_VEC_BYTES", 0);
   ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
+  ctx->opt[KVX_OPT_PDL] = env_or("KVX_PDL", 1);
   *out = ctx;
   return KVX_OK;
 }
@@ -587,6 +608,7 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
     case KVX_OPT_VEC_BYTES: if (value != 0 && value != 16 && value != 32) return KVX_EINVAL; break;
     case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
+    case KVX_OPT_PDL: if (value < 0 || value > 1) return KVX_EINVAL; break;
     default: break;
   }
   ctx->opt[option] = value;

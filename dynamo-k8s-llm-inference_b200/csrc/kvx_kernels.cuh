@@ -140,6 +140,13 @@ __device__ __forceinline__ void bulk_wait() {
   asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 
+// Programmatic dependent launch: a kernel launched with the stream-serialization attribute may become
+// resident while the previous kernel on the stream is still draining; nothing it reads or writes in
+// global memory may be touched before grid_dep_wait() returns (= the previous grid has completed and
+// its writes are visible).  Both are no-ops for a normally launched kernel.
+__device__ __forceinline__ void grid_dep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 template <int VEC>
 struct Vec;
 template <>
@@ -287,6 +294,7 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
   const unsigned cons_warps = (blockDim.x >> 5) - 1u;
   const unsigned S = p.stages;
 
+  grid_dep_launch_dependents();
   if (tid == 0) {
     for (unsigned s = 0; s < S; ++s) {
       mbar_init(&full_bar[s], 1u);
@@ -303,6 +311,7 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
   if (warp == 0) {
     // ------------------------------ producer ------------------------------
     const unsigned long long pol = p.l2_hint ? l2_policy_evict_first() : 0ull;
+    grid_dep_wait();
     RawItem raw{};
     if (lane < my_items) item_load(p, bid + lane * grid, raw);
     for (unsigned base = 0; base < my_items; base += 32u) {
@@ -355,6 +364,7 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
       // A stage is handed back one item late so that two stores stay in flight per thread.
       unsigned prev_stage = 0;
       bool have_prev = false;
+      grid_dep_wait();
       for (unsigned it = 0; it < my_items; ++it) {
         const unsigned s = it % S;
         mbar_wait(&full_bar[s], (it / S) & 1u);
@@ -390,6 +400,7 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
         const unsigned x = u / upr;
         doff[k] = dst_run_offset(p, x) + (u % upr) * VEC;
       }
+      grid_dep_wait();
       for (unsigned it = 0; it < my_items; ++it) {
         const unsigned s = it % S;
         mbar_wait(&full_bar[s], (it / S) & 1u);
@@ -420,6 +431,7 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
 // ----------------------------------------------------------------------------------------------
 template <int VEC, int KMAX>
 __global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
+  grid_dep_launch_dependents();
   const unsigned tid = threadIdx.x;
   const unsigned lane = tid & 31u;
   const unsigned T = blockDim.x;
@@ -437,6 +449,7 @@ __global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
   const unsigned bid = blockIdx.x;
   const unsigned grid = gridDim.x;
   const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+  grid_dep_wait();
   RawItem raw{};
   if (lane < my_items) item_load(p, bid + lane * grid, raw);
   for (unsigned base = 0; base < my_items; base += 32u) {

@@ -55,7 +55,10 @@ enum {
   KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
   KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16)                          */
   KVX_OPT_L2_HINT = 7,     /* 1: evict_first on loads                                        */
-  KVX_OPT__COUNT = 8
+  KVX_OPT_PDL = 8,         /* 1 (default): programmatic dependent launch — a transfer kernel may
+                              become resident while the previous kernel on the stream drains; it
+                              still waits for that kernel to complete before touching memory    */
+  KVX_OPT__COUNT = 9
 };
 
 typedef struct kvx_ctx kvx_ctx;

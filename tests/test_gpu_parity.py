@@ -385,3 +385,31 @@ def test_cuda_graph_capture_and_replay(ctx):
         assert np.array_equal(ddst.bytes(), dst.buf)
         assert ctx.flag_poll(flags + 8 * 9, 2)
     ctx.check()
+
+
+@pytest.mark.parametrize("pdl", [0, 1], ids=["serial", "pdl"])
+@pytest.mark.parametrize("engine", ["tma", "ldg"])
+def test_dependent_chain_back_to_back(engine, pdl):
+    """Eight handoffs queued back to back, each reading the blocks the previous one wrote, with
+    programmatic dependent launch on and off: a kernel that became resident early must still see
+    everything its predecessor stored (and the predecessor's completion flag must come first)."""
+    c = kvx.Context(0, engine=engine, pdl=pdl)
+    L, H, D, n, hops = 2, 8, 128, 24, 8
+    nb = n + 7
+    layouts = [o.HND, o.NHD]
+    pools = [o.make_pool(L, H, D, nb, layouts[k % 2], seed=77, fill="canary" if k else "random") for k in range(hops + 1)]
+    tabs = [o.make_table(nb, n, 300 + k) for k in range(hops + 1)]
+    devs = [DevPool(c, p) for p in pools]
+    dtabs = [dev_table(t) for t in tabs]
+    flags, _ = c.flags()
+    c.flag_reset(flags + 8 * 3, 0)
+    torch.cuda.synchronize()
+    for k in range(hops):
+        c.handoff_fused(devs[k].kp, dtabs[k], devs[k + 1].kp, dtabs[k + 1], n, flag=flags + 8 * 3, flag_val=k + 1)
+    torch.cuda.synchronize()
+    assert c.flag_poll(flags + 8 * 3, hops)
+    for k in range(hops):
+        o.handoff(pools[k], tabs[k], pools[k + 1], tabs[k + 1])
+        assert np.array_equal(devs[k + 1].bytes(), pools[k + 1].buf), f"hop {k}"
+    c.check()
+    c.close()
