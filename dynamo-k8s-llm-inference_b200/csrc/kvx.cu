@@ -68,6 +68,7 @@ struct kvx_ctx {
   uint32_t counter_cursor = 0;
   uint32_t table_cursor = 0;
   cudaStream_t aux = nullptr;
+  bool force_sys_fence = false;  // KVX_FORCE_SYS_FENCE=1: system-scope fences everywhere (debugging aid)
   std::string last_error;
   std::map<void*, std::string> imported;  // imported pointer → handle key ("" = same process)
   std::map<const void*, size_t> smem_limit;  // kernel → dynamic shared memory limit already set
@@ -199,7 +200,22 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   bool copy_mode = false;  // contiguous→contiguous bytes (kvx_copy)
   bool dst_is_peer = true;  // unknown destinations are treated as remote
   uint64_t copy_bytes = 0;
+  // kvx_handoff_host: block ids still in host memory (ns source ids, nd destination ids) that may
+  // ride in the kernel's parameter block, and the caller's pinned completion word (device alias).
+  const int32_t* h_src_tab = nullptr;
+  const int32_t* h_dst_tab = nullptr;
+  uint32_t ns = 0, nd = 0;
+  uint64_t* flag2 = nullptr;
 };
+
+// launch_xfer's answer when the host tables cannot ride in the parameters (engine / geometry / size):
+// the caller uploads them and launches with device tables instead.
+constexpr int32_t kNoParamTables = 1;
+// Measured on B200 (tools/e2e_host.py): up to 512 ids the parameter block beats the two uploads by
+// 3-5 us per request; beyond that the lanes' divergent reads of a table that no longer fits the
+// constant cache stall the producer (+7 us at 1024 ids, +40 us at 4096), so longer lists are uploaded.
+constexpr uint32_t kParamTabSmall = 128, kParamTabMax = 512;
+static_assert(sizeof(kvx::XferParamsTab<kParamTabMax>) <= 4096 - 64, "stay inside the classic 4 KiB parameter block");
 
 bool all_aligned(uint64_t a, const Plan& pl, const XferSide& s, const XferSide& d) {
   auto m = [a](uint64_t v) { return (v % a) == 0; };
@@ -223,9 +239,9 @@ int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
 // One launch.  With `pdl` the kernel is allowed to become resident while the previous kernel on the
 // stream is still draining (programmatic dependent launch); the kernels wait for that kernel's
 // completion themselves before they touch global memory (grid_dep_wait in kvx_kernels.cuh).
-template <typename K>
+template <typename K, typename P>
 cudaError_t launch_kernel(K kernel, uint32_t grid, uint32_t block, size_t smem, cudaStream_t stream, bool pdl,
-                          const XferParams& p) {
+                          const P& p) {
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(block);
@@ -237,6 +253,26 @@ cudaError_t launch_kernel(K kernel, uint32_t grid, uint32_t block, size_t smem, 
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1u : 0u;
   return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
+// The default kernel with the request's block ids copied into its parameter block: no H2D copy, no
+// copy-engine hand-over before the launch.
+template <int NT>
+int32_t launch_ptab(kvx_ctx* ctx, const XferParams& p, const LaunchSpec& ls, uint32_t grid, uint32_t block, size_t smem,
+                    cudaStream_t stream, bool pdl) {
+  auto k = kvx::kvx_xfer_tma_ptab_kernel<16, 8, NT>;
+  int32_t rc = set_smem(ctx, k, smem);
+  if (rc) return rc;
+  kvx::XferParamsTab<NT> pt;
+  pt.p = p;
+  pt.p.src.table = nullptr;
+  pt.p.dst.table = nullptr;
+  pt.p.src.tab_off = 0;
+  pt.p.dst.tab_off = ls.ns;
+  memcpy(pt.tab, ls.h_src_tab, ls.ns * sizeof(int));
+  memcpy(pt.tab + ls.ns, ls.h_dst_tab, ls.nd * sizeof(int));
+  KVX_CUDA(ctx, launch_kernel(k, grid, block, smem, stream, pdl, pt));
+  return KVX_OK;
 }
 
 int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>* src_bases,
@@ -303,6 +339,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     if (ls.flag) {  // empty request (full prefix hit): notify only
       KVX_CUDA(ctx, cudaMemcpyAsync(ls.flag, &ls.flag_val, sizeof(uint64_t), cudaMemcpyHostToDevice, stream));
     }
+    if (ls.flag2) KVX_CUDA(ctx, cudaMemcpyAsync(ls.flag2, &ls.flag_val, sizeof(uint64_t), cudaMemcpyDefault, stream));
     return KVX_OK;
   }
   if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;
@@ -314,10 +351,12 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.stages = stages; p.stage_bytes = stage_bytes;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
   p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
-  // Device-scope fences are enough when nobody outside this GPU observes the flag: the flag is one of
-  // this context's own slots and the destination pool was not imported from a peer.
-  p.flag_local = (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags && !ls.dst_is_peer &&
-                  env_or("KVX_FORCE_SYS_FENCE", 0) == 0) ? 1u : 0u;
+  // Fence scopes (finish_and_flag): per CTA device-wide when the data stays on this GPU, and to the
+  // end device-wide when the flag is one of this context's own slots and no second word is written.
+  p.flag2 = reinterpret_cast<unsigned long long*>(ls.flag2);
+  p.data_local = (!ls.dst_is_peer && !ctx->force_sys_fence) ? 1u : 0u;
+  p.flag_local = (p.data_local && ls.flag2 == nullptr &&
+                  (ls.flag == nullptr || (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags))) ? 1u : 0u;
   p.flag_val = ls.flag_val;
   p.status = ctx->d_status;
   p.done_counter = ctx->d_counters + (ctx->counter_cursor++ % kNumCounters);
@@ -332,6 +371,13 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
 
   const uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
   const uint32_t grid = std::min<uint32_t>(max_ctas, p.total_items);
+
+  if (ls.h_src_tab != nullptr) {
+    // Host tables ride in the parameters only with the default kernel (TMA engine, 16-byte thread stores).
+    const bool dflt_kernel = engine == kEngineTma && store_mode != 2 && vec_opt == 16 &&
+                             static_cast<uint64_t>(cons_warps) * 32u * 8u * 16u >= pl.piece_bytes;
+    if (!dflt_kernel || ls.ns + ls.nd > kParamTabMax) return kNoParamTables;
+  }
 
   if (engine == kEngineTma) {
     const bool dst_single_run = pl.d_runs == 1;
@@ -354,10 +400,17 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
         if (rc) return rc;
         KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
       } else if (static_cast<uint64_t>(T) * 8u * 16u >= pl.piece_bytes) {
-        auto k = kvx::kvx_xfer_tma_kernel<16, 8>;
-        int32_t rc = set_smem(ctx, k, smem);
-        if (rc) return rc;
-        KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
+        if (ls.h_src_tab != nullptr) {
+          const uint32_t entries = ls.ns + ls.nd;
+          int32_t rc = entries <= kParamTabSmall ? launch_ptab<kParamTabSmall>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
+                                                 : launch_ptab<kParamTabMax>(ctx, p, ls, grid, 32u + T, smem, stream, pdl);
+          if (rc) return rc;
+        } else {
+          auto k = kvx::kvx_xfer_tma_kernel<16, 8>;
+          int32_t rc = set_smem(ctx, k, smem);
+          if (rc) return rc;
+          KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
+        }
       } else {
         return KVX_EINVAL;  // stage larger than the consumer threads can drain: raise CONSUMER_WARPS
       }
@@ -515,6 +568,41 @@ int32_t unmap_ptr(kvx_ctx* ctx, void* ptr) {
   return KVX_OK;
 }
 
+struct HostTables {
+  const int32_t* src;
+  const int32_t* dst;
+  uint32_t ns, nd;
+};
+
+// The fused handoff behind kvx_handoff_fused (device tables) and kvx_handoff_host (host tables `ht`,
+// tried first as kernel parameters; completion word `flag2`).
+int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table, const kvx_pool* dst,
+                     const int32_t* d_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag, uint64_t flag_val,
+                     void* stream, const HostTables* ht, const void* /*unused*/, uint64_t* flag2) {
+  if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
+  uint32_t so, dof, hc, sl;
+  int32_t rc = resolve_xform(&src->desc, &dst->desc, xf, &so, &dof, &hc, &sl, src->desc.layout);
+  if (rc) return rc;
+  const kvx_pool_desc& s = src->desc;
+  const kvx_pool_desc& d = dst->desc;
+  LaunchSpec ls;
+  ls.src = paged_side(src, d_src_table);
+  ls.dst = paged_side(dst, d_dst_table);
+  ls.n = n; ls.regions = s.regions;
+  ls.N = std::min(s.block_tokens, d.block_tokens);  // granule = the smaller block
+  ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
+  ls.sg = ChunkGeom{s.layout, s.heads, so, s.block_tokens};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
+  ls.flag = flag;
+  ls.flag_val = flag_val;
+  ls.flag2 = flag2;
+  ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
+  if (ht) {
+    ls.h_src_tab = ht->src; ls.h_dst_tab = ht->dst; ls.ns = ht->ns; ls.nd = ht->nd;
+  }
+  return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
+}
+
 }  // namespace
 
 // =================================================================================================
@@ -575,6 +663,8 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
   ctx->opt[KVX_OPT_PDL] = env_or("KVX_PDL", 1);
+  ctx->opt[KVX_OPT_PARAM_TABLES] = env_or("KVX_PARAM_TABLES", 1);
+  ctx->force_sys_fence = env_or("KVX_FORCE_SYS_FENCE", 0) != 0;
   *out = ctx;
   return KVX_OK;
 }
@@ -609,6 +699,7 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
     case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PDL: if (value < 0 || value > 1) return KVX_EINVAL; break;
+    case KVX_OPT_PARAM_TABLES: if (value < 0 || value > 1) return KVX_EINVAL; break;
     default: break;
   }
   ctx->opt[option] = value;
@@ -905,25 +996,8 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
                           const int32_t* d_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag,
                           uint64_t flag_val, void* stream) {
   if (!ctx || !src || !dst) return KVX_EINVAL;
-  if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
   if (n != 0 && (!d_src_table || !d_dst_table)) return KVX_EINVAL;
-  uint32_t so, dof, hc, sl;
-  int32_t rc = resolve_xform(&src->desc, &dst->desc, xf, &so, &dof, &hc, &sl, src->desc.layout);
-  if (rc) return rc;
-  const kvx_pool_desc& s = src->desc;
-  const kvx_pool_desc& d = dst->desc;
-  LaunchSpec ls;
-  ls.src = paged_side(src, d_src_table);
-  ls.dst = paged_side(dst, d_dst_table);
-  ls.n = n; ls.regions = s.regions;
-  ls.N = std::min(s.block_tokens, d.block_tokens);  // granule = the smaller block
-  ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{s.layout, s.heads, so, s.block_tokens};
-  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
-  ls.flag = flag;
-  ls.flag_val = flag_val;
-  ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
-  return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
+  return handoff_impl(ctx, src, d_src_table, dst, d_dst_table, n, xf, flag, flag_val, stream, nullptr, nullptr, nullptr);
 }
 
 int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table, const kvx_pool* dst,
@@ -932,6 +1006,7 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
   if (!ctx || !src || !dst) return KVX_EINVAL;
   if (n > KVX_MAX_HOST_TABLE) return KVX_ERANGE;
   if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
+  if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DeviceGuard guard(ctx->device);
   // The peer may own the destination blocks: ids are validated here against each pool's size so a
@@ -941,20 +1016,40 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
     if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->desc.num_blocks) return KVX_ERANGE;
   for (uint32_t i = 0; i < nd; ++i)
     if (h_dst_table[i] < 0 || static_cast<uint64_t>(h_dst_table[i]) >= dst->desc.num_blocks) return KVX_ERANGE;
-  int* d_src = nullptr;
-  int* d_dst = nullptr;
-  if (n != 0) {
-    if (ctx->table_cursor + static_cast<uint64_t>(ns) + nd > kTableRing) ctx->table_cursor = 0;
-    d_src = ctx->d_table_ring + ctx->table_cursor;
-    d_dst = d_src + ns;
-    ctx->table_cursor += ns + nd;
-    KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, ns * sizeof(int), cudaMemcpyHostToDevice, st));
-    KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, nd * sizeof(int), cudaMemcpyHostToDevice, st));
-  }
-  uint64_t* f = flag ? flag : ctx->d_flags + (kNumFlags - 1);
-  int32_t rc = kvx_handoff_fused(ctx, src, d_src, dst, d_dst, n, xf, f, flag_val, stream);
-  if (rc) return rc;
+
+  // Completion word: pinned (or registered) host memory is written by the kernel itself through its
+  // device alias; pageable memory gets a D2H copy of the flag after the kernel.
+  uint64_t* done_dev = nullptr;
   if (h_done) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, h_done) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+      done_dev = static_cast<uint64_t*>(at.devicePointer);
+    else
+      (void)cudaGetLastError();
+  }
+  uint64_t* f = flag ? flag : ((h_done && !done_dev) ? ctx->d_flags + (kNumFlags - 1) : nullptr);
+
+  int32_t rc = kNoParamTables;
+  if (n != 0 && ctx->opt[KVX_OPT_PARAM_TABLES] != 0 && static_cast<uint64_t>(ns) + nd <= kParamTabMax) {
+    // Short lists ride in the kernel's parameter block: one launch, no copy-engine work.
+    HostTables ht{h_src_table, h_dst_table, ns, nd};
+    rc = handoff_impl(ctx, src, nullptr, dst, nullptr, n, xf, f, flag_val, stream, &ht, nullptr, done_dev);
+  }
+  if (rc == kNoParamTables) {
+    int* d_src = nullptr;
+    int* d_dst = nullptr;
+    if (n != 0) {
+      if (ctx->table_cursor + static_cast<uint64_t>(ns) + nd > kTableRing) ctx->table_cursor = 0;
+      d_src = ctx->d_table_ring + ctx->table_cursor;
+      d_dst = d_src + ns;
+      ctx->table_cursor += ns + nd;
+      KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, ns * sizeof(int), cudaMemcpyHostToDevice, st));
+      KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, nd * sizeof(int), cudaMemcpyHostToDevice, st));
+    }
+    rc = handoff_impl(ctx, src, d_src, dst, d_dst, n, xf, f, flag_val, stream, nullptr, nullptr, done_dev);
+  }
+  if (rc) return rc;
+  if (h_done && !done_dev) {
     // A peer flag is readable through the same mapping the kernel wrote it through.
     KVX_CUDA(ctx, cudaMemcpyAsync(h_done, f, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
   }

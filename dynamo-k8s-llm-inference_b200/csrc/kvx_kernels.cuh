@@ -36,6 +36,8 @@ struct XferSide {
   unsigned int piece_stride;        // bytes between consecutive pieces of one chunk
   unsigned int ratio;               // paged: granules per block on this side (block-size regrouping), >= 1
   unsigned int sub_stride;          // paged: bytes between consecutive granules inside one block
+  unsigned int tab_off;             // paged, tables carried in the kernel parameters: first entry of this side's ids
+  unsigned int reserved;
 };
 
 struct XferParams {
@@ -52,8 +54,10 @@ struct XferParams {
   unsigned int d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b;
   unsigned int stages, stage_bytes;
   unsigned int l2_hint;
-  unsigned int flag_local;   // 1: flag and destination live on this GPU → device-scope fences suffice
+  unsigned int data_local;   // 1: every destination byte lands in THIS GPU's memory → a device-scope fence per CTA publishes it
+  unsigned int flag_local;   // 1: the flag lives on this GPU too and nobody outside it observes it → device scope to the end
   unsigned long long* flag;  // completion flag (local or peer memory) or null
+  unsigned long long* flag2; // second completion word (e.g. the caller's pinned host memory) or null
   unsigned long long flag_val;
   unsigned int* done_counter;  // scratch: CTAs finished (zero on entry, zero again on exit)
   unsigned int* status;        // scratch: sticky error bits
@@ -206,12 +210,24 @@ struct RawItem {
   unsigned w, r, i, piece;
 };
 
-__device__ __forceinline__ void side_load(const XferSide& s, unsigned r, unsigned i, RawSide& out) {
+// Where the block ids come from: device memory (the caller's tables), or the kernel's own parameter
+// block (kvx_handoff_host copies short host lists there, so no H2D copy precedes the launch).
+struct TabGlobal {
+  __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const {
+    return s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
+  }
+};
+struct TabParam {
+  const int* tab;  // address of the table array inside the __grid_constant__ parameter
+  __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const { return tab[s.tab_off + blk]; }
+};
+
+template <class Tab>
+__device__ __forceinline__ void side_load(const XferSide& s, const Tab& tab, unsigned r, unsigned i, RawSide& out) {
   out.id = 0;
   out.base = 0;
   if (s.bases != nullptr) {
-    const unsigned blk = i / s.ratio;
-    out.id = s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
+    out.id = tab.get(s, i / s.ratio);
     out.base = __ldg(s.bases + r);
   }
 }
@@ -232,14 +248,15 @@ __device__ __forceinline__ unsigned long long side_finish(const XferSide& s, con
   return a + s.slice_off + static_cast<unsigned long long>(piece) * s.piece_stride;
 }
 
-__device__ __forceinline__ void item_load(const XferParams& p, unsigned w, RawItem& raw) {
+template <class Tab>
+__device__ __forceinline__ void item_load(const XferParams& p, const Tab& tab, unsigned w, RawItem& raw) {
   raw.w = w;
   raw.piece = w % p.ppc;
   const unsigned c = w / p.ppc;
   raw.i = c % p.n;
   raw.r = c / p.n;
-  side_load(p.src, raw.r, raw.i, raw.s);
-  side_load(p.dst, raw.r, raw.i, raw.d);
+  side_load(p.src, tab, raw.r, raw.i, raw.s);
+  side_load(p.dst, tab, raw.r, raw.i, raw.d);
 }
 
 __device__ __forceinline__ void item_finish(const XferParams& p, const RawItem& raw, unsigned long long& sa,
@@ -258,20 +275,26 @@ __device__ __forceinline__ unsigned dst_run_offset(const XferParams& p, unsigned
   return (x / p.d_n1) * p.d_stride_a + (x % p.d_n1) * p.d_stride_b;
 }
 
-// Completion: every CTA publishes its stores system-wide, the last one to finish release-stores the
-// flag (H6) and re-zeroes the counter for the next launch that gets this counter slot.
+// Completion (H6): every CTA publishes its stores, the last one to finish stores the flag(s) and
+// re-zeroes the counter for the next launch that gets this counter slot.  Scopes: the per-CTA fence is
+// device-wide when the data lands in this GPU's own memory (its L2 is the point of coherence for
+// every observer, local or remote) and system-wide when the stores crossed NVLink; the last CTA's
+// fence is system-wide unless the flag itself stays on this GPU.
 __device__ __forceinline__ void finish_and_flag(const XferParams& p) {
-  if (p.flag == nullptr) return;
-  // bar.sync orders every thread's stores before thread 0's system-scope fence, which is cumulative
-  // (the pattern cooperative-groups grid sync uses): one fence per CTA instead of one per thread.
+  if (p.flag == nullptr && p.flag2 == nullptr) return;
+  // bar.sync orders every thread's stores before thread 0's fence, which is cumulative (the pattern
+  // cooperative-groups grid sync uses): one fence per CTA instead of one per thread.
   __syncthreads();
   if (threadIdx.x == 0) {
-    if (p.flag_local) __threadfence(); else __threadfence_system();
+    if (p.data_local) __threadfence(); else __threadfence_system();
     const unsigned prev = atomicAdd(p.done_counter, 1u);
     if (prev == gridDim.x - 1) {
       if (p.flag_local) __threadfence(); else __threadfence_system();
       *p.done_counter = 0u;
-      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+      if (p.flag != nullptr)
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+      if (p.flag2 != nullptr)
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag2), "l"(p.flag_val) : "memory");
     }
   }
 }
@@ -280,8 +303,8 @@ __device__ __forceinline__ void finish_and_flag(const XferParams& p) {
 // TMA engine.  blockDim.x = 32 * (1 + consumer warps); warp 0 produces.
 // STORE: 16 / 32 = vector stores of that many bytes by the consumer threads; 0 = bulk stores.
 // ----------------------------------------------------------------------------------------------
-template <int STORE, int KMAX>
-__global__ void kvx_xfer_tma_kernel(const XferParams p) {
+template <int STORE, int KMAX, class Tab>
+__device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab) {
   extern __shared__ __align__(1024) unsigned char stage_mem[];
   __shared__ __align__(8) unsigned long long full_bar[kMaxStages];
   __shared__ __align__(8) unsigned long long empty_bar[kMaxStages];
@@ -313,13 +336,13 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
     const unsigned long long pol = p.l2_hint ? l2_policy_evict_first() : 0ull;
     grid_dep_wait();
     RawItem raw{};
-    if (lane < my_items) item_load(p, bid + lane * grid, raw);
+    if (lane < my_items) item_load(p, tab, bid + lane * grid, raw);
     for (unsigned base = 0; base < my_items; base += 32u) {
       unsigned long long sa = 0, da = 0;
       unsigned bytes = 0;
       if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
       // next batch's lookups travel while this batch is issued
-      if (base + 32u + lane < my_items) item_load(p, bid + (base + 32u + lane) * grid, raw);
+      if (base + 32u + lane < my_items) item_load(p, tab, bid + (base + 32u + lane) * grid, raw);
       const unsigned cnt = min(32u, my_items - base);
       for (unsigned j = 0; j < cnt; ++j) {
         const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
@@ -426,11 +449,28 @@ __global__ void kvx_xfer_tma_kernel(const XferParams p) {
   finish_and_flag(p);
 }
 
+template <int STORE, int KMAX>
+__global__ void kvx_xfer_tma_kernel(const __grid_constant__ XferParams p) {
+  xfer_tma_body<STORE, KMAX>(p, TabGlobal{});
+}
+
+// The same kernel with the request's block ids inside the parameter block (NT int32 entries: the
+// source side's ids from tab_off of p.src, the destination side's from tab_off of p.dst).
+template <int NT>
+struct XferParamsTab {
+  XferParams p;
+  int tab[NT];
+};
+template <int STORE, int KMAX, int NT>
+__global__ void kvx_xfer_tma_ptab_kernel(const __grid_constant__ XferParamsTab<NT> pt) {
+  xfer_tma_body<STORE, KMAX>(pt.p, TabParam{pt.tab});
+}
+
 // ----------------------------------------------------------------------------------------------
 // LDG engine: no shared memory; each thread owns KMAX vector units of every piece.
 // ----------------------------------------------------------------------------------------------
 template <int VEC, int KMAX>
-__global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
+__global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const __grid_constant__ XferParams p) {
   grid_dep_launch_dependents();
   const unsigned tid = threadIdx.x;
   const unsigned lane = tid & 31u;
@@ -450,13 +490,14 @@ __global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const XferParams p) {
   const unsigned grid = gridDim.x;
   const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
   grid_dep_wait();
+  const TabGlobal tab{};
   RawItem raw{};
-  if (lane < my_items) item_load(p, bid + lane * grid, raw);
+  if (lane < my_items) item_load(p, tab, bid + lane * grid, raw);
   for (unsigned base = 0; base < my_items; base += 32u) {
     unsigned long long sa = 0, da = 0;
     unsigned bytes = 0;
     if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
-    if (base + 32u + lane < my_items) item_load(p, bid + (base + 32u + lane) * grid, raw);
+    if (base + 32u + lane < my_items) item_load(p, tab, bid + (base + 32u + lane) * grid, raw);
     const unsigned cnt = min(32u, my_items - base);
     for (unsigned j = 0; j < cnt; ++j) {
       const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);

@@ -58,7 +58,10 @@ enum {
   KVX_OPT_PDL = 8,         /* 1 (default): programmatic dependent launch — a transfer kernel may
                               become resident while the previous kernel on the stream drains; it
                               still waits for that kernel to complete before touching memory    */
-  KVX_OPT__COUNT = 9
+  KVX_OPT_PARAM_TABLES = 9, /* 1 (default): kvx_handoff_host carries lists of up to 512 ids (both
+                               sides together) in the kernel's parameter block instead of
+                               uploading them first                                              */
+  KVX_OPT__COUNT = 10
 };
 
 typedef struct kvx_ctx kvx_ctx;
@@ -181,9 +184,12 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
                           const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);
 
 /* The call a serving engine makes per request ([vllm] kv_transfer_params, scheduler.py:664-674):
- * block-id lists arrive in HOST memory.  Uploads both tables into context scratch, runs the fused
- * handoff, and — when `h_done` is not NULL — copies the completion flag back into *h_done (pinned
- * or pageable host memory) on the same stream.  n is bounded by KVX_MAX_HOST_TABLE. */
+ * block-id lists arrive in HOST memory.  Lists of up to 512 ids (both sides together, i.e. prompts
+ * up to 4k tokens at 16-token blocks) travel in the kernel's parameter block — one launch, no copy
+ * before it; longer ones are uploaded into context scratch first.  When `h_done` is not NULL it receives flag_val once every byte has landed: pinned
+ * (cudaHostAlloc / cudaHostRegister) memory is written by the kernel itself, pageable memory by a
+ * D2H copy queued behind it on the same stream.  The lists are consumed before the call returns.
+ * n is bounded by KVX_MAX_HOST_TABLE. */
 #define KVX_MAX_HOST_TABLE (1u << 20)
 int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table,
                          const kvx_pool* dst, const int32_t* h_dst_table, uint32_t n,

@@ -413,3 +413,45 @@ def test_dependent_chain_back_to_back(engine, pdl):
         assert np.array_equal(devs[k + 1].bytes(), pools[k + 1].buf), f"hop {k}"
     c.check()
     c.close()
+
+
+@pytest.mark.parametrize("n", [1, 63, 64, 65, 255, 256, 257, 300])
+@pytest.mark.parametrize("param_tables", [1, 0], ids=["ptab", "upload"])
+def test_host_entry_table_transport(param_tables, n):
+    """kvx_handoff_host moves short id lists inside the kernel's parameter block (<= 128 and <= 512 ids
+    in two size classes) and uploads longer ones; the completion word lands in pinned memory (written
+    by the kernel) or pageable memory (copied back).  Same bytes either way."""
+    c = kvx.Context(0, param_tables=param_tables)
+    nb = n + 11
+    src = o.make_pool(1, 8, 64, nb, o.HND, seed=n)
+    dst = o.make_pool(1, 8, 64, nb + 2, o.NHD, fill="canary")
+    ts, td = o.make_table(nb, n, 5), o.make_table(nb + 2, n, 6)
+    dsrc, ddst = DevPool(c, src), DevPool(c, dst)
+    pinned = torch.zeros(2, dtype=torch.int64).pin_memory()
+    pageable = np.zeros(2, dtype=np.int64)
+    flags, _ = c.flags()
+    c.flag_reset(flags + 8 * 7, 0)
+    c.handoff_host(dsrc.kp, ts, ddst.kp, td, n, flag=flags + 8 * 7, flag_val=41, h_done=pinned[1:])
+    torch.cuda.synchronize()
+    assert int(pinned[1]) == 41 and int(pinned[0]) == 0 and c.flag_poll(flags + 8 * 7, 41)
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    # second request into the same pools: pageable completion word, no device flag
+    ts2, td2 = o.make_table(nb, n, 15), o.make_table(nb + 2, n, 16)
+    c.handoff_host(dsrc.kp, ts2, ddst.kp, td2, n, flag=None, flag_val=42, h_done=pageable[1:])
+    torch.cuda.synchronize()
+    assert pageable[1] == 42 and pageable[0] == 0
+    o.handoff(src, ts2, dst, td2)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    # empty request: notify only, both kinds of completion word
+    c.handoff_host(dsrc.kp, None, ddst.kp, None, 0, flag=flags + 8 * 7, flag_val=43, h_done=pinned[:1])
+    torch.cuda.synchronize()
+    assert int(pinned[0]) == 43 and c.flag_poll(flags + 8 * 7, 43)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    bad = td.copy()
+    bad[0] = nb + 2
+    with pytest.raises(kvx.KvxError) as e:
+        c.handoff_host(dsrc.kp, ts, ddst.kp, bad, n)
+    assert e.value.code == kvx.api.ERANGE
+    c.check()
+    c.close()
