@@ -211,11 +211,13 @@ struct LaunchSpec {  // what a transfer needs besides geometry
 // launch_xfer's answer when the host tables cannot ride in the parameters (engine / geometry / size):
 // the caller uploads them and launches with device tables instead.
 constexpr int32_t kNoParamTables = 1;
-// Measured on B200 (tools/e2e_host.py): up to 512 ids the parameter block beats the two uploads by
-// 3-5 us per request; beyond that the lanes' divergent reads of a table that no longer fits the
-// constant cache stall the producer (+7 us at 1024 ids, +40 us at 4096), so longer lists are uploaded.
-constexpr uint32_t kParamTabSmall = 128, kParamTabMax = 512;
-static_assert(sizeof(kvx::XferParamsTab<kParamTabMax>) <= 4096 - 64, "stay inside the classic 4 KiB parameter block");
+// Four size classes of the parameter block (ids of both sides together).  Measured on B200
+// (tools/e2e_host.py): with the ids read by generic loads the host-table entry costs the same as the
+// device-table entry at every size up to the 32 KiB parameter limit, 5-6 us less per request than
+// uploading the lists first.  (Indexed constant-bank reads were tried first: the 32 lanes of a lookup
+// want 32 different entries and the constant cache serves one address at a time, +40 us at 4096 ids.)
+constexpr uint32_t kParamTabSmall = 128, kParamTabMid = 512, kParamTabBig = 2048, kParamTabMax = 8000;
+static_assert(sizeof(kvx::XferParamsTab<kParamTabMax>) <= 32764, "kernel parameter block limit (CUDA 12.1+, sm_70+)");
 
 bool all_aligned(uint64_t a, const Plan& pl, const XferSide& s, const XferSide& d) {
   auto m = [a](uint64_t v) { return (v % a) == 0; };
@@ -376,7 +378,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     // Host tables ride in the parameters only with the default kernel (TMA engine, 16-byte thread stores).
     const bool dflt_kernel = engine == kEngineTma && store_mode != 2 && vec_opt == 16 &&
                              static_cast<uint64_t>(cons_warps) * 32u * 8u * 16u >= pl.piece_bytes;
-    if (!dflt_kernel || ls.ns + ls.nd > kParamTabMax) return kNoParamTables;
+    if (!dflt_kernel || ls.ns + ls.nd > std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES])) return kNoParamTables;
   }
 
   if (engine == kEngineTma) {
@@ -403,6 +405,8 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
         if (ls.h_src_tab != nullptr) {
           const uint32_t entries = ls.ns + ls.nd;
           int32_t rc = entries <= kParamTabSmall ? launch_ptab<kParamTabSmall>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
+                       : entries <= kParamTabMid ? launch_ptab<kParamTabMid>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
+                       : entries <= kParamTabBig ? launch_ptab<kParamTabBig>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
                                                  : launch_ptab<kParamTabMax>(ctx, p, ls, grid, 32u + T, smem, stream, pdl);
           if (rc) return rc;
         } else {
@@ -663,7 +667,7 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
   ctx->opt[KVX_OPT_PDL] = env_or("KVX_PDL", 1);
-  ctx->opt[KVX_OPT_PARAM_TABLES] = env_or("KVX_PARAM_TABLES", 1);
+  ctx->opt[KVX_OPT_PARAM_TABLES] = env_or("KVX_PARAM_TABLES", 8000);
   ctx->force_sys_fence = env_or("KVX_FORCE_SYS_FENCE", 0) != 0;
   *out = ctx;
   return KVX_OK;
@@ -699,7 +703,7 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
     case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PDL: if (value < 0 || value > 1) return KVX_EINVAL; break;
-    case KVX_OPT_PARAM_TABLES: if (value < 0 || value > 1) return KVX_EINVAL; break;
+    case KVX_OPT_PARAM_TABLES: if (value < 0 || value > kParamTabMax) return KVX_EINVAL; break;
     default: break;
   }
   ctx->opt[option] = value;
@@ -1030,7 +1034,7 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
   uint64_t* f = flag ? flag : ((h_done && !done_dev) ? ctx->d_flags + (kNumFlags - 1) : nullptr);
 
   int32_t rc = kNoParamTables;
-  if (n != 0 && ctx->opt[KVX_OPT_PARAM_TABLES] != 0 && static_cast<uint64_t>(ns) + nd <= kParamTabMax) {
+  if (n != 0 && static_cast<int64_t>(ns) + nd <= std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES])) {
     // Short lists ride in the kernel's parameter block: one launch, no copy-engine work.
     HostTables ht{h_src_table, h_dst_table, ns, nd};
     rc = handoff_impl(ctx, src, nullptr, dst, nullptr, n, xf, f, flag_val, stream, &ht, nullptr, done_dev);

@@ -218,8 +218,14 @@ struct TabGlobal {
   }
 };
 struct TabParam {
-  const int* tab;  // address of the table array inside the __grid_constant__ parameter
-  __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const { return tab[s.tab_off + blk]; }
+  const int* tab;  // generic address of the table array inside the __grid_constant__ parameter
+  // A generic load, not an indexed constant-bank read: the 32 lanes of a lookup want 32 different
+  // entries, which the constant cache would serve one address at a time.
+  __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const {
+    int v;
+    asm volatile("ld.s32 %0, [%1];" : "=r"(v) : "l"(tab + s.tab_off + blk));
+    return v;
+  }
 };
 
 template <class Tab>

@@ -58,9 +58,9 @@ enum {
   KVX_OPT_PDL = 8,         /* 1 (default): programmatic dependent launch — a transfer kernel may
                               become resident while the previous kernel on the stream drains; it
                               still waits for that kernel to complete before touching memory    */
-  KVX_OPT_PARAM_TABLES = 9, /* 1 (default): kvx_handoff_host carries lists of up to 512 ids (both
-                               sides together) in the kernel's parameter block instead of
-                               uploading them first                                              */
+  KVX_OPT_PARAM_TABLES = 9, /* kvx_handoff_host carries lists of up to this many ids (both sides
+                               together; default and maximum 8000, 0 = never) in the kernel's
+                               parameter block instead of uploading them first                   */
   KVX_OPT__COUNT = 10
 };
 
@@ -184,8 +184,8 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
                           const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);
 
 /* The call a serving engine makes per request ([vllm] kv_transfer_params, scheduler.py:664-674):
- * block-id lists arrive in HOST memory.  Lists of up to 512 ids (both sides together, i.e. prompts
- * up to 4k tokens at 16-token blocks) travel in the kernel's parameter block — one launch, no copy
+ * block-id lists arrive in HOST memory.  Lists of up to 8000 ids (both sides together, i.e. prompts
+ * up to 64k tokens at 16-token blocks) travel in the kernel's parameter block — one launch, no copy
  * before it; longer ones are uploaded into context scratch first.  When `h_done` is not NULL it receives flag_val once every byte has landed: pinned
  * (cudaHostAlloc / cudaHostRegister) memory is written by the kernel itself, pageable memory by a
  * D2H copy queued behind it on the same stream.  The lists are consumed before the call returns.

@@ -415,12 +415,12 @@ def test_dependent_chain_back_to_back(engine, pdl):
     c.close()
 
 
-@pytest.mark.parametrize("n", [1, 63, 64, 65, 255, 256, 257, 300])
-@pytest.mark.parametrize("param_tables", [1, 0], ids=["ptab", "upload"])
+@pytest.mark.parametrize("n", [1, 63, 64, 65, 255, 256, 257, 1023, 1024, 1025, 3999, 4000, 4001])
+@pytest.mark.parametrize("param_tables", [8000, 0], ids=["ptab", "upload"])
 def test_host_entry_table_transport(param_tables, n):
-    """kvx_handoff_host moves short id lists inside the kernel's parameter block (<= 128 and <= 512 ids
-    in two size classes) and uploads longer ones; the completion word lands in pinned memory (written
-    by the kernel) or pageable memory (copied back).  Same bytes either way."""
+    """kvx_handoff_host moves id lists inside the kernel's parameter block (size classes of 128, 512,
+    2048 and 8000 ids for both sides together) and uploads longer ones; the completion word lands in
+    pinned memory (written by the kernel) or pageable memory (copied back).  Same bytes either way."""
     c = kvx.Context(0, param_tables=param_tables)
     nb = n + 11
     src = o.make_pool(1, 8, 64, nb, o.HND, seed=n)

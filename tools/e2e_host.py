@@ -20,7 +20,7 @@ def wall(fn, reps=50):
         torch.cuda.synchronize()
         best = min(best, (time.perf_counter()-t0)/reps)
     return best
-for n in (8, 64, 128, 200, 256, 512, 2048):
+for n in (8, 64, 256, 512, 1024, 2048):
     if n > nb-1: continue
     hs = [np.ascontiguousarray((1+rng.permutation(nb-1)[:n]).astype(np.int32)) for _ in range(4)]
     hd = [np.ascontiguousarray((1+rng.permutation(nb-1)[:n]).astype(np.int32)) for _ in range(4)]
@@ -35,7 +35,7 @@ for n in (8, 64, 128, 200, 256, 512, 2048):
       "host_pageable_done": lambda k: ctx.handoff_host(P.pool, hs[k%4], D.pool, hd[k%4], n, None, flags, k+1, done_pg[k%64:k%64+1], stream),
       "host_no_done": lambda k: ctx.handoff_host(P.pool, hs[k%4], D.pool, hd[k%4], n, None, flags, k+1, None, stream),
     }
-    for pt in (1, 0):
+    for pt in (8000, 0):
         ctx.set_option("param_tables", pt)
         for name, fn in cases.items():
             if name.startswith("device") and pt == 0: continue
