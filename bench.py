@@ -12,8 +12,8 @@ A step = one request's handoff (all layers, K and V) from a prefill pool to a de
           the blocks over NVLink (--mode push: the prefill GPU stores them instead).  No collective
           on the data path ("scaling": "weak").
 value = payload GB/s of the whole job (all pairs), inputs resident in HBM; e2e = the same through
-kvx_handoff_host with host block-id lists (H2D of the tables and D2H of the completion word inside
-the timed region).  --impl reference times the CPU memcpy handoff (oracle/kvx_oracle.c) instead.
+kvx_handoff_host with host block-id lists (the ids' trip to the GPU and the completion word's trip
+back to pinned host memory inside the timed region).  --impl reference times the CPU memcpy handoff (oracle/kvx_oracle.c) instead.
 """
 from __future__ import annotations
 
@@ -395,7 +395,8 @@ def run_single(args):
         "dtype": "u8 (opaque bf16 bits)", "data": "synthetic", "config": workload_config(1, shape, isl),
         "e2e": {"value": round(args.steps * payload / e2e_s / 1e9, 2), "unit": UNIT, "h2d_bytes_per_step": 8 * n,
                 "d2h_bytes_per_step": 8, "ms_per_step": round(1e3 * e2e_s / args.steps, 4),
-                "through": "kvx_handoff_host (C ABI): host int32 block-id lists in, completion word out; the KV "
+                "through": "kvx_handoff_host (C ABI): host int32 block-id lists in (carried in the kernel's parameter "
+                           "block), completion word out (written by the kernel into pinned host memory); the KV "
                            "payload is produced by prefill in HBM and never crosses PCIe on this path"},
         "gpu_launches": int(launches),
         "clocks": clocks,
@@ -625,7 +626,7 @@ def run_pairs(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="kvx", choices=["kvx", "reference"])
     ap.add_argument("--isl", type=int, default=8192)
