@@ -429,8 +429,11 @@ def run_pairs(args):
     local = int(os.environ.get("LOCAL_RANK", rank))
     assert world == args.gpus and world % 2 == 0, "pairs need an even number of ranks"
     torch.cuda.set_device(local)
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
+    # stdout carries exactly one JSON line: everything native libraries print there (NCCL's version
+    # banner) is sent to stderr by pointing fd 1 at fd 2 for the whole run; the line goes to the saved fd.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{local}"))
     hbm_peak, peak_src = load_peaks()
     shape = kvx.KV_SHAPES["meta-llama/Llama-3.1-8B"]
@@ -616,7 +619,8 @@ def run_pairs(args):
             "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
             "direction": args.mode, "landed_ok": bool(ok[0] > 0), "staged_path": staged,
         }
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
+    os.close(json_fd)
     dist.barrier()
     w.close()
     dist.destroy_process_group()
