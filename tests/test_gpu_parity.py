@@ -455,3 +455,66 @@ def test_host_entry_table_transport(param_tables, n):
     assert e.value.code == kvx.api.ERANGE
     c.check()
     c.close()
+
+
+def _cross_layer_nhd_pool(L, H, D, nb, fill, seed=0, N=16, E=2):
+    """vLLM's cross-layer block pool in NHD order: one allocation (num_blocks, num_layers, 2, N, H, D)
+    ([vllm] v1/attention/backends/flash_attn.py:158-160).  As a kvx pool: region (l, kv) starts at
+    (2l + kv) * chunk and every block id advances by the whole cross-layer block."""
+    chunk = N * H * D * E
+    if fill == "random":
+        words = np.random.Generator(np.random.PCG64(seed)).integers(0, 65536, size=nb * 2 * L * chunk // 2, dtype=np.uint16)
+    else:
+        words = np.full(nb * 2 * L * chunk // 2, o.CANARY16, dtype=np.uint16)
+    return o.Pool(words.view(np.uint8).copy(), [r * chunk for r in range(2 * L)], nb, 2 * L * chunk, N, H, D, E, o.NHD)
+
+
+def test_cross_layer_block_pools(cfg_ctx):
+    """Cross-layer block pools on either side, against split per-layer pools on the other, and the
+    result checked twice: against the oracle and against numpy indexing of the 6-d array itself."""
+    L, H, D, n, nb = 3, 8, 128, 21, 40
+    src = _cross_layer_nhd_pool(L, H, D, nb, "random", seed=9)
+    dst = o.make_pool(L, H, D, nb + 3, o.HND, fill="canary")
+    ts, td = o.make_table(nb, n, 1), o.make_table(nb + 3, n, 2)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n)
+    torch.cuda.synchronize()
+    got = ddst.bytes()
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(got, dst.buf)
+    a6 = src.buf.view(np.uint16).reshape(nb, L, 2, 16, H, D)                    # the engine's own view
+    g5 = got.view(np.uint16).reshape(2 * L, nb + 3, H, 16, D)                   # split HND regions
+    for l in range(L):
+        for kv in range(2):
+            assert np.array_equal(g5[2 * l + kv, td], a6[ts, l, kv].transpose(0, 2, 1, 3))
+    # and back into a cross-layer pool
+    back = _cross_layer_nhd_pool(L, H, D, nb, "canary")
+    dback = DevPool(cfg_ctx, back)
+    cfg_ctx.handoff_fused(ddst.kp, dev_table(td), dback.kp, dev_table(ts), n)
+    torch.cuda.synchronize()
+    b6 = dback.bytes().view(np.uint16).reshape(nb, L, 2, 16, H, D)
+    assert np.array_equal(b6[ts], a6[ts])
+    rest = np.ones(nb, dtype=bool)
+    rest[ts] = False
+    assert (b6[rest] == o.CANARY16).all()
+
+
+@pytest.mark.parametrize("N", [16, 64])
+def test_mla_latent_pools(cfg_ctx, N):
+    """MLA-style caches: one latent vector per token and layer (no separate V, a single 'head' of
+    512 + 64 elements) — one region per layer, 1152-byte rows; block sizes 16 and 64."""
+    L, Dl, n, nb = 5, 576, 13, 20
+    chunk = N * Dl * 2
+    words = np.random.Generator(np.random.PCG64(3)).integers(0, 65536, size=L * nb * chunk // 2, dtype=np.uint16)
+    src = o.Pool(words.view(np.uint8).copy(), [r * nb * chunk for r in range(L)], nb, chunk, N, 1, Dl, 2, o.NHD)
+    dst = o.Pool(np.full(L * (nb + 1) * chunk // 2, o.CANARY16, dtype=np.uint16).view(np.uint8).copy(),
+                 [r * (nb + 1) * chunk for r in range(L)], nb + 1, chunk, N, 1, Dl, 2, o.HND)
+    ts, td = o.make_table(nb, n, 4), o.make_table(nb + 1, n, 5)
+    dsrc, ddst = DevPool(cfg_ctx, src), DevPool(cfg_ctx, dst)
+    cfg_ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n)
+    torch.cuda.synchronize()
+    o.handoff(src, ts, dst, td)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    s3 = src.buf.view(np.uint16).reshape(L, nb, N * Dl)
+    d3 = ddst.bytes().view(np.uint16).reshape(L, nb + 1, N * Dl)
+    assert np.array_equal(d3[:, td], s3[:, ts])          # with one head NHD and HND are the same bytes
