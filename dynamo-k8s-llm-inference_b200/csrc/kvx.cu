@@ -233,6 +233,12 @@ template <typename K>
 int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
   size_t& have = ctx->smem_limit[reinterpret_cast<const void*>(kernel)];
   if (have >= bytes) return KVX_OK;
+  cudaFuncAttributes fa{};
+  KVX_CUDA(ctx, cudaFuncGetAttributes(&fa, kernel));  // another context or kvx_handoff_static may have raised it already
+  if (static_cast<size_t>(fa.maxDynamicSharedSizeBytes) >= bytes) {
+    have = static_cast<size_t>(fa.maxDynamicSharedSizeBytes);
+    return KVX_OK;
+  }
   KVX_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)));
   have = bytes;
   return KVX_OK;
@@ -1103,8 +1109,13 @@ int32_t static_setup(int device, StaticDevice** out) {
       (void)cudaGetLastError();
       return KVX_ECUDA;
     }
-    e = cudaFuncSetAttribute(kvx::kvx_xfer_tma_kernel<16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             static_cast<int>(kStaticStages * kStaticStageBytes));
+    // Raise the kernel's dynamic shared-memory limit to what this entry needs, never lower it: a
+    // context on the same device may already have raised it further for a deeper pipeline.
+    cudaFuncAttributes fa{};
+    e = cudaFuncGetAttributes(&fa, kvx::kvx_xfer_tma_kernel<16, 8>);
+    if (e == cudaSuccess && fa.maxDynamicSharedSizeBytes < static_cast<int>(kStaticStages * kStaticStageBytes))
+      e = cudaFuncSetAttribute(kvx::kvx_xfer_tma_kernel<16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(kStaticStages * kStaticStageBytes));
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, device);
     if (e != cudaSuccess) {
       (void)cudaGetLastError();

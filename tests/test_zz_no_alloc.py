@@ -40,7 +40,10 @@ def test_static_entry_matches_host_entry_twice():
     t_ref, t_new = _device_copy(dst), _device_copy(dst)   # existing entry point / new entry point
     flag = torch.zeros(2, dtype=torch.int64, device="cuda")
 
-    ctx = kvx.Context(0)
+    # The existing entry runs with a deeper pipeline (128 KiB of shared memory) than the static entry
+    # (64 KiB) on the same kernel: the static entry's one-time set-up must not lower the kernel's
+    # shared-memory limit under this context, or its second launch below would fail.
+    ctx = kvx.Context(0, stages=4, stage_bytes=32768, consumer_warps=16)
     p_src, p_ref = _registered(ctx, t_src, src), _registered(ctx, t_ref, dst)
     (d_src, keep1), (d_new, keep2) = _desc(t_src, src), _desc(t_new, dst)
 
