@@ -26,6 +26,7 @@ namespace {
 constexpr uint32_t kNumFlags = 4096;     // completion flags per context (uint64 each)
 constexpr uint32_t kNumCounters = 1024;  // done-counter ring (one per launch that carries a flag)
 constexpr uint32_t kTableRing = 1u << 22;  // int32 entries of device scratch for host block tables
+constexpr uint64_t kNvlinkInFlightBytes = 8ull << 20;  // 6 MiB in flight saturate one NVLink direction (tools/footprint.py); margin for a busy switch
 constexpr uint32_t kMemMagic = 0x4d58564bu;   // "KVXM"
 constexpr uint32_t kPoolMagic = 0x5058564bu;  // "KVXP"
 
@@ -198,7 +199,9 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   uint64_t* flag = nullptr;
   uint64_t flag_val = 0;
   bool copy_mode = false;  // contiguous→contiguous bytes (kvx_copy)
-  bool dst_is_peer = true;  // unknown destinations are treated as remote
+  bool dst_is_peer = true;  // unknown destinations are treated as remote (fence scope)
+  bool dst_is_peer_known = false;  // the destination is KNOWN to be a peer's memory (launch geometry)
+  bool src_is_peer = false;        // the source is known to be a peer's memory
   uint64_t copy_bytes = 0;
   // kvx_handoff_host: block ids still in host memory (ns source ids, nd destination ids) that may
   // ride in the kernel's parameter block, and the caller's pinned completion word (device alias).
@@ -289,10 +292,19 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (!guard.ok) return cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice");
 
   int engine = static_cast<int>(ctx->opt[KVX_OPT_ENGINE]);
-  const uint32_t stages = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGES]);
-  const uint32_t stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
+  // Pipeline geometry, 0 = choose here.  A transfer whose bytes stay on this GPU is HBM-bound and wants
+  // every SM: 4 x 16 KiB stages, two CTAs per SM (profiles/r01_sweep_*).  A transfer with one side in a
+  // peer's memory is NVLink-bound: ~6 MiB in flight saturate the link (tools/footprint.py), so it runs
+  // deep pipelines (6 x 32 KiB) in few CTAs and leaves most SMs to the decode steps beside it.
+  const bool remote = ls.src_is_peer || ls.dst_is_peer_known;
+  uint32_t stages = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGES]);
+  uint32_t stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
   uint32_t cons_warps = static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]);
-  const uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
+  uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
+  const bool auto_stages = stages == 0, auto_stage_bytes = stage_bytes == 0;
+  if (stage_bytes == 0) stage_bytes = remote ? 32768u : 16384u;
+  if (stages == 0) stages = remote ? 6u : 4u;
+  if (ctas_per_sm == 0) ctas_per_sm = remote ? 1u : 2u;
   const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
   int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);
   const bool pdl = ctx->opt[KVX_OPT_PDL] != 0;
@@ -356,6 +368,13 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.s_runs = pl.s_runs; p.s_run_bytes = pl.s_run_bytes; p.s_stride = pl.s_stride;
   p.d_runs = pl.d_runs; p.d_run_bytes = pl.d_run_bytes; p.d_n1 = pl.d_n1;
   p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
+  // small pieces (TP shards) keep fewer bytes per stage in flight: shrink the stages to the piece and
+  // deepen the ring within the same shared-memory budget
+  if (remote && auto_stages && auto_stage_bytes && engine == kEngineTma && pl.piece_bytes * 2u <= stage_bytes) {
+    const uint32_t budget = stages * stage_bytes;
+    stage_bytes = (pl.piece_bytes + 1023u) / 1024u * 1024u;
+    stages = std::min<uint32_t>(static_cast<uint32_t>(kvx::kMaxStages), budget / stage_bytes);
+  }
   p.stages = stages; p.stage_bytes = stage_bytes;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
   p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
@@ -377,7 +396,15 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (vec_opt == 0) vec_opt = 16;  // measured: 16-byte stores beat 32-byte ones on B200 for this path
   if (vec_opt == 32 && !ok32) vec_opt = 16;
 
-  const uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
+  uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
+  // A serving engine that runs decode steps next to the handoff bounds the SMs the transfer occupies.
+  if (ctx->opt[KVX_OPT_MAX_CTAS] > 0) {
+    max_ctas = std::min<uint32_t>(max_ctas, static_cast<uint32_t>(ctx->opt[KVX_OPT_MAX_CTAS]));
+  } else if (remote && engine == kEngineTma) {
+    const uint64_t in_flight_per_cta = static_cast<uint64_t>(stages) * pl.piece_bytes;
+    const uint32_t need = static_cast<uint32_t>((kNvlinkInFlightBytes + in_flight_per_cta - 1) / in_flight_per_cta);
+    max_ctas = std::min<uint32_t>(max_ctas, std::max<uint32_t>(16u, need));
+  }
   const uint32_t grid = std::min<uint32_t>(max_ctas, p.total_items);
 
   if (ls.h_src_tab != nullptr) {
@@ -607,6 +634,8 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.flag_val = flag_val;
   ls.flag2 = flag2;
   ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
+  ls.dst_is_peer_known = ls.dst_is_peer;
+  ls.src_is_peer = !src->imported_ptrs.empty() || src->ctx != ctx;
   if (ht) {
     ls.h_src_tab = ht->src; ls.h_dst_tab = ht->dst; ls.ns = ht->ns; ls.nd = ht->nd;
   }
@@ -665,15 +694,16 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->d_status = ctx->d_counters + kNumCounters;
   if (cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking) != cudaSuccess) return fail(KVX_ECUDA);
   ctx->opt[KVX_OPT_ENGINE] = env_or("KVX_ENGINE", 0);
-  ctx->opt[KVX_OPT_STAGES] = env_or("KVX_STAGES", 4);
-  ctx->opt[KVX_OPT_STAGE_BYTES] = env_or("KVX_STAGE_BYTES", 16384);
-  ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 2);
+  ctx->opt[KVX_OPT_STAGES] = env_or("KVX_STAGES", 0);
+  ctx->opt[KVX_OPT_STAGE_BYTES] = env_or("KVX_STAGE_BYTES", 0);
+  ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 0);
   ctx->opt[KVX_OPT_STORE_MODE] = env_or("KVX_STORE_MODE", 0);
   ctx->opt[KVX_OPT_VEC_BYTES] = env_or("KVX_VEC_BYTES", 0);
   ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
   ctx->opt[KVX_OPT_PDL] = env_or("KVX_PDL", 1);
   ctx->opt[KVX_OPT_PARAM_TABLES] = env_or("KVX_PARAM_TABLES", 8000);
+  ctx->opt[KVX_OPT_MAX_CTAS] = env_or("KVX_MAX_CTAS", 0);
   ctx->force_sys_fence = env_or("KVX_FORCE_SYS_FENCE", 0) != 0;
   *out = ctx;
   return KVX_OK;
@@ -701,15 +731,16 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
   if (!ctx || option < 0 || option >= KVX_OPT__COUNT) return KVX_EINVAL;
   switch (option) {
     case KVX_OPT_ENGINE: if (value < 0 || value > 2) return KVX_EINVAL; break;
-    case KVX_OPT_STAGES: if (value < 1 || value > kvx::kMaxStages) return KVX_EINVAL; break;
-    case KVX_OPT_STAGE_BYTES: if (value < 1024 || value > 200 * 1024 || value % 1024) return KVX_EINVAL; break;
-    case KVX_OPT_CTAS_PER_SM: if (value < 1 || value > 32) return KVX_EINVAL; break;
+    case KVX_OPT_STAGES: if (value < 0 || value > kvx::kMaxStages) return KVX_EINVAL; break;
+    case KVX_OPT_STAGE_BYTES: if (value != 0 && (value < 1024 || value > 200 * 1024 || value % 1024)) return KVX_EINVAL; break;
+    case KVX_OPT_CTAS_PER_SM: if (value < 0 || value > 32) return KVX_EINVAL; break;
     case KVX_OPT_STORE_MODE: if (value < 0 || value > 2) return KVX_EINVAL; break;
     case KVX_OPT_VEC_BYTES: if (value != 0 && value != 16 && value != 32) return KVX_EINVAL; break;
     case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PDL: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PARAM_TABLES: if (value < 0 || value > kParamTabMax) return KVX_EINVAL; break;
+    case KVX_OPT_MAX_CTAS: if (value < 0 || value > 65535) return KVX_EINVAL; break;
     default: break;
   }
   ctx->opt[option] = value;
@@ -995,6 +1026,15 @@ int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint6
   ls.copy_bytes = bytes;
   ls.flag = flag;
   ls.flag_val = flag_val;
+  if (bytes != 0) {  // a side that lives on another GPU makes this an NVLink transfer (launch geometry only)
+    DeviceGuard guard(ctx->device);
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->device)
+      ls.src_is_peer = true;
+    if (cudaPointerGetAttributes(&at, dst) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->device)
+      ls.dst_is_peer_known = true;
+    (void)cudaGetLastError();
+  }
   if (bytes == 0) {
     if (flag) return kvx_flag_reset(ctx, flag, flag_val, stream);
     return KVX_OK;

@@ -16,7 +16,7 @@ from ._lib import PoolDesc, XformC, c_i32, c_i64, c_sz, c_u32, c_u64, c_vp
 
 NHD, HND = 0, 1
 OPT = {"engine": 0, "stages": 1, "stage_bytes": 2, "ctas_per_sm": 3, "store_mode": 4, "vec_bytes": 5,
-       "consumer_warps": 6, "l2_hint": 7, "pdl": 8, "param_tables": 9}
+       "consumer_warps": 6, "l2_hint": 7, "pdl": 8, "param_tables": 9, "max_ctas": 10}
 ENGINE = {"auto": 0, "ldg": 1, "tma": 2}
 OK, EINVAL, ECUDA, ENOMEM, EUNSUPPORTED, ETIMEOUT, ERANGE, EIPC, ENOTREADY = 0, -1, -2, -3, -4, -5, -6, -7, -8
 

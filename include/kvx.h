@@ -48,9 +48,11 @@ enum { KVX_LAYOUT_NHD = 0, KVX_LAYOUT_HND = 1 };
 /* Tunables for kvx_ctx_set_option (also read once from the environment as KVX_<NAME>). */
 enum {
   KVX_OPT_ENGINE = 0,      /* 0 auto, 1 "ldg" (register path), 2 "tma" (bulk-copy pipeline) */
-  KVX_OPT_STAGES = 1,      /* tma: pipeline stages (2..8)                                    */
-  KVX_OPT_STAGE_BYTES = 2, /* tma: bytes per stage (multiple of 1024)                        */
-  KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this                                   */
+  KVX_OPT_STAGES = 1,      /* tma: pipeline stages (1..8); 0 (default) = 4 for transfers that stay
+                              on this GPU, 6..8 when one side is a peer's memory               */
+  KVX_OPT_STAGE_BYTES = 2, /* tma: bytes per stage (multiple of 1024); 0 (default) = 16 KiB
+                              on-GPU, 32 KiB over NVLink                                       */
+  KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this; 0 (default) = 2 on-GPU, 1 over NVLink */
   KVX_OPT_STORE_MODE = 4,  /* tma: 0 auto, 1 thread stores, 2 bulk stores                    */
   KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
   KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16)                          */
@@ -61,7 +63,12 @@ enum {
   KVX_OPT_PARAM_TABLES = 9, /* kvx_handoff_host carries lists of up to this many ids (both sides
                                together; default and maximum 8000, 0 = never) in the kernel's
                                parameter block instead of uploading them first                   */
-  KVX_OPT__COUNT = 10
+  KVX_OPT_MAX_CTAS = 10,    /* upper bound on the CTAs (hence SMs) one transfer occupies.  0 (default):
+                               every SM for transfers that stay on this GPU (HBM-bound); for a
+                               transfer over NVLink just enough CTAs to keep 8 MiB in flight
+                               (43 of 148 SMs at 32 KiB chunks; 6 MiB saturate the link), so that
+                               the rest of the GPU stays free for work running beside it         */
+  KVX_OPT__COUNT = 11
 };
 
 typedef struct kvx_ctx kvx_ctx;
