@@ -24,7 +24,7 @@ PY
 }
 L8=meta-llama/Llama-3.1-8B
 L70=meta-llama/Llama-3.1-70B
-if [ "$NGPU" -ge 2 ]; then
+if [ "$NGPU" -ge 2 ] && [ -z "${SKIP_CFG3:-}" ]; then
   run cfg3_1p1d_c1 $L8 'kvx://local?prefill=1&decode=1&isl=8192&requests=64&concurrency=1&layout=nhd'
   run cfg3_1p1d_c4 $L8 'kvx://local?prefill=1&decode=1&isl=8192&requests=64&concurrency=4&layout=nhd'
   run cfg3_1p1d_isl1k_c4 $L8 'kvx://local?prefill=1&decode=1&isl=1024&requests=128&concurrency=4&layout=nhd'
@@ -32,12 +32,12 @@ fi
 if [ "$NGPU" -ge 6 ]; then
   run cfg4_tp4_tp2_hnd $L70 'kvx://local?prefill=1&decode=1&ptp=4&dtp=2&isl=8192&requests=16&concurrency=1'
   run cfg4_tp4_tp2_hnd_c2 $L70 'kvx://local?prefill=1&decode=1&ptp=4&dtp=2&isl=8192&requests=16&concurrency=2'
+  run cfg4_tp2_tp4_hnd $L70 'kvx://local?prefill=1&decode=1&ptp=2&dtp=4&isl=8192&requests=16&concurrency=1'
   run cfg4_tp4_tp2_nhd $L70 'kvx://local?prefill=1&decode=1&ptp=4&dtp=2&isl=8192&requests=16&concurrency=1&layout=nhd'
 fi
 if [ "$NGPU" -ge 8 ]; then
   run cfg5_4p4d_isl8k $L8 'kvx://local?prefill=4&decode=4&isl=8192&requests=32&concurrency=1&layout=nhd'
   run cfg5_4p4d_mixed $L8 'kvx://local?prefill=4&decode=4&isl=1024,2048,4096,8192,16384,32768&requests=32&concurrency=1&layout=nhd'
-  run cfg5_4p4d_mixed_c2 $L8 'kvx://local?prefill=4&decode=4&isl=1024,2048,4096,8192,16384,32768&requests=32&concurrency=2&layout=nhd'
 fi
 if [ "$NGPU" -ge 5 ]; then
   run incast_4p_to_1d $L8 'kvx://local?prefill=4&decode=1&isl=8192&requests=16&concurrency=4&route=spread'
