@@ -36,6 +36,8 @@ ENGINE_CONFIGS = [
     dict(engine="tma", store_mode=1, vec_bytes=32, stages=3, stage_bytes=32768, consumer_warps=8),
     dict(engine="tma", store_mode=2, stages=4, stage_bytes=8192, consumer_warps=2),
     dict(engine="tma", store_mode=2, stages=6, stage_bytes=32768, consumer_warps=8, ctas_per_sm=2, l2_hint=1),
+    dict(engine="tma", max_ctas=5, pdl=0),          # bounded SM footprint, plain launches
+    dict(engine="tma", stages=6, stage_bytes=32768, ctas_per_sm=1, max_ctas=43),   # the geometry NVLink transfers default to
 ]
 
 

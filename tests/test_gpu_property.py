@@ -16,7 +16,9 @@ _ctxs = {}
 
 def _ctx(engine):
     if engine not in _ctxs:
-        opts = dict(engine="ldg") if engine == "ldg" else dict(engine="tma", store_mode={"tma": 0, "tma_bulk": 2}[engine])
+        opts = {"ldg": dict(engine="ldg"), "tma": dict(engine="tma", store_mode=0), "tma_bulk": dict(engine="tma", store_mode=2),
+                # host-table entry: ids in the kernel parameter block, a handful of CTAs, no dependent launch
+                "tma_host": dict(engine="tma", max_ctas=3, pdl=0)}[engine]
         _ctxs[engine] = kvx.Context(0, **opts)
     return _ctxs[engine]
 
@@ -29,7 +31,7 @@ geometry = st.fixed_dictionaries(dict(
     arr_d=st.sampled_from(["split", "blocks_first"]), n=st.integers(1, 40), seed=st.integers(0, 2**20)))
 
 
-@pytest.mark.parametrize("engine", ["tma", "tma_bulk", "ldg"])
+@pytest.mark.parametrize("engine", ["tma", "tma_bulk", "ldg", "tma_host"])
 @settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture, HealthCheck.too_slow])
 @given(g=geometry)
 def test_random_geometry_matches_oracle(engine, g):
@@ -46,7 +48,10 @@ def test_random_geometry_matches_oracle(engine, g):
     dst = o.make_pool(g["L"], Hd, g["D"], nd + 4, g["ld"], block_tokens=Nd, elem_bytes=g["E"], arrangement=g["arr_d"], fill="canary")
     ts, td = o.make_table(ns + 3, ns, g["seed"] + 1), o.make_table(nd + 4, nd, g["seed"] + 2)
     dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
-    ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n, kvx.Xform(g["so"], g["do"], g["Hc"], g["ld"]))
+    if engine == "tma_host":
+        ctx.handoff_host(dsrc.kp, ts, ddst.kp, td, n, kvx.Xform(g["so"], g["do"], g["Hc"], g["ld"]))
+    else:
+        ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n, kvx.Xform(g["so"], g["do"], g["Hc"], g["ld"]))
     torch.cuda.synchronize()
     ctx.check()
     o.handoff_regroup(src, ts, dst, td, o.Xform(g["so"], g["do"], g["Hc"]), n_small=n)
