@@ -209,7 +209,15 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   const int32_t* h_dst_tab = nullptr;
   uint32_t ns = 0, nd = 0;
   uint64_t* flag2 = nullptr;
+  // kvx_handoff_batch: (address, value) pairs the last CTA stores, carried next to the ids
+  const uint64_t* notify = nullptr;
+  uint32_t notify_count = 0;
 };
+
+// int32 entries of the parameter table area a launch needs: both sides' ids, then the notifications
+uint32_t param_entries(const LaunchSpec& ls) {
+  return ls.notify_count ? ((ls.ns + ls.nd + 1u) & ~1u) + 4u * ls.notify_count : ls.ns + ls.nd;
+}
 
 // launch_xfer's answer when the host tables cannot ride in the parameters (engine / geometry / size):
 // the caller uploads them and launches with device tables instead.
@@ -282,6 +290,12 @@ int32_t launch_ptab(kvx_ctx* ctx, const XferParams& p, const LaunchSpec& ls, uin
   pt.p.dst.tab_off = ls.ns;
   memcpy(pt.tab, ls.h_src_tab, ls.ns * sizeof(int));
   memcpy(pt.tab + ls.ns, ls.h_dst_tab, ls.nd * sizeof(int));
+  if (ls.notify_count != 0) {
+    const uint32_t off = (ls.ns + ls.nd + 1u) & ~1u;  // 8-byte aligned inside the int32 array
+    pt.p.notify_off = off;
+    pt.p.notify_count = ls.notify_count;
+    memcpy(pt.tab + off, ls.notify, static_cast<size_t>(ls.notify_count) * 2 * sizeof(uint64_t));
+  }
   KVX_CUDA(ctx, launch_kernel(k, grid, block, smem, stream, pdl, pt));
   return KVX_OK;
 }
@@ -382,7 +396,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   // end device-wide when the flag is one of this context's own slots and no second word is written.
   p.flag2 = reinterpret_cast<unsigned long long*>(ls.flag2);
   p.data_local = (!ls.dst_is_peer && !ctx->force_sys_fence) ? 1u : 0u;
-  p.flag_local = (p.data_local && ls.flag2 == nullptr &&
+  p.flag_local = (p.data_local && ls.flag2 == nullptr && ls.notify_count == 0 &&
                   (ls.flag == nullptr || (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags))) ? 1u : 0u;
   p.flag_val = ls.flag_val;
   p.status = ctx->d_status;
@@ -411,7 +425,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     // Host tables ride in the parameters only with the default kernel (TMA engine, 16-byte thread stores).
     const bool dflt_kernel = engine == kEngineTma && store_mode != 2 && vec_opt == 16 &&
                              static_cast<uint64_t>(cons_warps) * 32u * 8u * 16u >= pl.piece_bytes;
-    if (!dflt_kernel || ls.ns + ls.nd > std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES])) return kNoParamTables;
+    if (!dflt_kernel || param_entries(ls) > std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES])) return kNoParamTables;
   }
 
   if (engine == kEngineTma) {
@@ -436,7 +450,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
         KVX_CUDA(ctx, launch_kernel(k, grid, 32u + T, smem, stream, pdl, p));
       } else if (static_cast<uint64_t>(T) * 8u * 16u >= pl.piece_bytes) {
         if (ls.h_src_tab != nullptr) {
-          const uint32_t entries = ls.ns + ls.nd;
+          const uint32_t entries = param_entries(ls);
           int32_t rc = entries <= kParamTabSmall ? launch_ptab<kParamTabSmall>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
                        : entries <= kParamTabMid ? launch_ptab<kParamTabMid>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
                        : entries <= kParamTabBig ? launch_ptab<kParamTabBig>(ctx, p, ls, grid, 32u + T, smem, stream, pdl)
@@ -610,12 +624,16 @@ struct HostTables {
   const int32_t* dst;
   uint32_t ns, nd;
 };
+struct NotifyList {
+  const uint64_t* pairs;  // (address, value) x count
+  uint32_t count;
+};
 
 // The fused handoff behind kvx_handoff_fused (device tables) and kvx_handoff_host (host tables `ht`,
 // tried first as kernel parameters; completion word `flag2`).
 int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table, const kvx_pool* dst,
                      const int32_t* d_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag, uint64_t flag_val,
-                     void* stream, const HostTables* ht, const void* /*unused*/, uint64_t* flag2) {
+                     void* stream, const HostTables* ht, const NotifyList* notify, uint64_t* flag2) {
   if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
   uint32_t so, dof, hc, sl;
   int32_t rc = resolve_xform(&src->desc, &dst->desc, xf, &so, &dof, &hc, &sl, src->desc.layout);
@@ -638,6 +656,9 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.src_is_peer = !src->imported_ptrs.empty() || src->ctx != ctx;
   if (ht) {
     ls.h_src_tab = ht->src; ls.h_dst_tab = ht->dst; ls.ns = ht->ns; ls.nd = ht->nd;
+  }
+  if (notify) {
+    ls.notify = notify->pairs; ls.notify_count = notify->count;
   }
   return launch_xfer(ctx, ls, &src->base, &dst->base, static_cast<cudaStream_t>(stream));
 }
@@ -1102,6 +1123,66 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
   if (h_done && !done_dev) {
     // A peer flag is readable through the same mapping the kernel wrote it through.
     KVX_CUDA(ctx, cudaMemcpyAsync(h_done, f, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  }
+  return KVX_OK;
+}
+
+int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, const kvx_batch_item* items,
+                          uint32_t count, const kvx_xform* xf, void* stream) {
+  if (!ctx || !src || !dst || (count != 0 && !items)) return KVX_EINVAL;
+  if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
+  if (count == 0) return KVX_OK;
+  uint64_t total = 0, notes = 0;
+  bool pinned_only = true;
+  DeviceGuard guard(ctx->device);
+  std::vector<uint64_t> pairs;
+  pairs.reserve(4 * static_cast<size_t>(count));
+  for (uint32_t k = 0; k < count; ++k) {
+    const kvx_batch_item& it = items[k];
+    if (it.n > KVX_MAX_HOST_TABLE) return KVX_ERANGE;
+    if (it.n != 0 && (!it.h_src_table || !it.h_dst_table)) return KVX_EINVAL;
+    for (uint32_t i = 0; i < it.n; ++i) {
+      if (it.h_src_table[i] < 0 || static_cast<uint64_t>(it.h_src_table[i]) >= src->desc.num_blocks) return KVX_ERANGE;
+      if (it.h_dst_table[i] < 0 || static_cast<uint64_t>(it.h_dst_table[i]) >= dst->desc.num_blocks) return KVX_ERANGE;
+    }
+    total += it.n;
+    if (it.flag) {
+      pairs.push_back(reinterpret_cast<uint64_t>(it.flag));
+      pairs.push_back(it.flag_val);
+    }
+    if (it.h_done) {
+      cudaPointerAttributes at{};
+      if (cudaPointerGetAttributes(&at, it.h_done) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer) {
+        pairs.push_back(reinterpret_cast<uint64_t>(at.devicePointer));
+        pairs.push_back(it.flag_val);
+      } else {
+        (void)cudaGetLastError();
+        pinned_only = false;
+      }
+    }
+  }
+  notes = pairs.size() / 2;
+  const bool one_launch = count > 1 && total != 0 && pinned_only && src->desc.block_tokens == dst->desc.block_tokens &&
+                          2 * total + 4 * notes + 1 <= static_cast<uint64_t>(std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES]));
+  if (one_launch) {
+    std::vector<int32_t> ids(2 * static_cast<size_t>(total));
+    size_t at = 0;
+    for (uint32_t k = 0; k < count; ++k) {
+      if (items[k].n) memcpy(ids.data() + at, items[k].h_src_table, items[k].n * sizeof(int32_t));
+      if (items[k].n) memcpy(ids.data() + total + at, items[k].h_dst_table, items[k].n * sizeof(int32_t));
+      at += items[k].n;
+    }
+    HostTables ht{ids.data(), ids.data() + total, static_cast<uint32_t>(total), static_cast<uint32_t>(total)};
+    NotifyList nl{pairs.data(), static_cast<uint32_t>(notes)};
+    int32_t rc = handoff_impl(ctx, src, nullptr, dst, nullptr, static_cast<uint32_t>(total), xf, nullptr, 0, stream, &ht,
+                              notes ? &nl : nullptr, nullptr);
+    if (rc != kNoParamTables) return rc;
+  }
+  // one request per launch: same bytes, same notifications
+  for (uint32_t k = 0; k < count; ++k) {
+    const kvx_batch_item& it = items[k];
+    int32_t rc = kvx_handoff_host(ctx, src, it.h_src_table, dst, it.h_dst_table, it.n, xf, it.flag, it.flag_val, it.h_done, stream);
+    if (rc) return rc;
   }
   return KVX_OK;
 }

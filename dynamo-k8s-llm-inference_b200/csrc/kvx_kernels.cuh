@@ -59,6 +59,9 @@ struct XferParams {
   unsigned long long* flag;  // completion flag (local or peer memory) or null
   unsigned long long* flag2; // second completion word (e.g. the caller's pinned host memory) or null
   unsigned long long flag_val;
+  // Batched requests (kvx_handoff_batch): notify_count (address, value) pairs of 64-bit words each, stored
+  // in the parameter block's table area from int32 entry notify_off (even), all written by the last CTA.
+  unsigned int notify_count, notify_off;
   unsigned int* done_counter;  // scratch: CTAs finished (zero on entry, zero again on exit)
   unsigned int* status;        // scratch: sticky error bits
 };
@@ -216,6 +219,7 @@ struct TabGlobal {
   __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const {
     return s.table ? __ldg(s.table + blk) : static_cast<int>(blk);
   }
+  __device__ __forceinline__ void notify(unsigned, unsigned, unsigned) const {}  // batches always carry their tables in the parameters
 };
 struct TabParam {
   const int* tab;  // generic address of the table array inside the __grid_constant__ parameter
@@ -225,6 +229,17 @@ struct TabParam {
     int v;
     asm volatile("ld.s32 %0, [%1];" : "=r"(v) : "l"(tab + s.tab_off + blk));
     return v;
+  }
+  // Store every batched request's completion word: the lanes of one warp share the list, each store a
+  // release at system scope (ordered after everything the last CTA observed before it got here).
+  __device__ __forceinline__ void notify(unsigned count, unsigned off, unsigned lane) const {
+    const unsigned long long* rec = reinterpret_cast<const unsigned long long*>(tab + off);
+    for (unsigned k = lane; k < count; k += 32u) {
+      unsigned long long addr, val;
+      asm volatile("ld.u64 %0, [%1];" : "=l"(addr) : "l"(rec + 2 * k));
+      asm volatile("ld.u64 %0, [%1];" : "=l"(val) : "l"(rec + 2 * k + 1));
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(addr), "l"(val) : "memory");
+    }
   }
 };
 
@@ -286,21 +301,30 @@ __device__ __forceinline__ unsigned dst_run_offset(const XferParams& p, unsigned
 // device-wide when the data lands in this GPU's own memory (its L2 is the point of coherence for
 // every observer, local or remote) and system-wide when the stores crossed NVLink; the last CTA's
 // fence is system-wide unless the flag itself stays on this GPU.
-__device__ __forceinline__ void finish_and_flag(const XferParams& p) {
-  if (p.flag == nullptr && p.flag2 == nullptr) return;
+template <class Tab>
+__device__ __forceinline__ void finish_and_flag(const XferParams& p, const Tab& tab) {
+  if (p.flag == nullptr && p.flag2 == nullptr && p.notify_count == 0u) return;
   // bar.sync orders every thread's stores before thread 0's fence, which is cumulative (the pattern
   // cooperative-groups grid sync uses): one fence per CTA instead of one per thread.
   __syncthreads();
-  if (threadIdx.x == 0) {
-    if (p.data_local) __threadfence(); else __threadfence_system();
-    const unsigned prev = atomicAdd(p.done_counter, 1u);
-    if (prev == gridDim.x - 1) {
-      if (p.flag_local) __threadfence(); else __threadfence_system();
-      *p.done_counter = 0u;
-      if (p.flag != nullptr)
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
-      if (p.flag2 != nullptr)
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag2), "l"(p.flag_val) : "memory");
+  if (threadIdx.x < 32u) {  // warp 0: lane 0 counts, all lanes share a batch's notifications
+    unsigned last = 0u;
+    if (threadIdx.x == 0) {
+      if (p.data_local) __threadfence(); else __threadfence_system();
+      const unsigned prev = atomicAdd(p.done_counter, 1u);
+      if (prev == gridDim.x - 1) {
+        last = 1u;
+        if (p.flag_local) __threadfence(); else __threadfence_system();
+        *p.done_counter = 0u;
+        if (p.flag != nullptr)
+          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+        if (p.flag2 != nullptr)
+          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag2), "l"(p.flag_val) : "memory");
+      }
+    }
+    if (p.notify_count != 0u) {
+      last = __shfl_sync(0xffffffffu, last, 0);  // also orders lane 0's fence before the other lanes' stores
+      if (last) tab.notify(p.notify_count, p.notify_off, threadIdx.x);
     }
   }
 }
@@ -452,7 +476,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
       }
     }
   }
-  finish_and_flag(p);
+  finish_and_flag(p, tab);
 }
 
 template <int STORE, int KMAX>
@@ -518,7 +542,7 @@ __global__ void __launch_bounds__(256) kvx_xfer_ldg_kernel(const __grid_constant
         if (tid + k * T < units) stg_stream(dst + doff[k], v[k]);
     }
   }
-  finish_and_flag(p);
+  finish_and_flag(p, tab);
 }
 
 // Stream-ordered, bounded wait on a completion flag written by another GPU.

@@ -31,6 +31,13 @@ class XformC(ctypes.Structure):
     _fields_ = [("src_head_off", c_u32), ("dst_head_off", c_u32), ("heads", c_u32), ("stage_layout", c_u32)]
 
 
+class BatchItem(ctypes.Structure):
+    """struct kvx_batch_item (include/kvx.h)."""
+
+    _fields_ = [("h_src_table", c_vp), ("h_dst_table", c_vp), ("n", c_u32), ("reserved", c_u32), ("flag", c_vp),
+                ("flag_val", c_u64), ("h_done", c_vp)]
+
+
 # name → (restype, argtypes): every symbol include/kvx.h declares
 PROTOTYPES = {
     "kvx_version": (c_u32, []),
@@ -62,6 +69,7 @@ PROTOTYPES = {
     "kvx_scatter": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp]),
     "kvx_handoff_fused": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp]),
     "kvx_handoff_host": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp, c_vp]),
+    "kvx_handoff_batch": (c_i32, [c_vp, c_vp, c_vp, P(BatchItem), c_u32, P(XformC), c_vp]),
     "kvx_handoff_static": (c_i32, [c_i32, P(PoolDesc), c_vp, P(PoolDesc), c_vp, c_u32, P(XformC), c_vp, c_u64, c_vp]),
 }
 

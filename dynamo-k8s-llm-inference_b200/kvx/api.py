@@ -12,7 +12,7 @@ from dataclasses import dataclass
 from typing import Optional, Sequence
 
 from . import _lib
-from ._lib import PoolDesc, XformC, c_i32, c_i64, c_sz, c_u32, c_u64, c_vp
+from ._lib import BatchItem, PoolDesc, XformC, c_i32, c_i64, c_sz, c_u32, c_u64, c_vp
 
 NHD, HND = 0, 1
 OPT = {"engine": 0, "stages": 1, "stage_bytes": 2, "ctas_per_sm": 3, "store_mode": 4, "vec_bytes": 5,
@@ -229,6 +229,27 @@ class Context:
         self._check(self.lib.kvx_handoff_host(self.handle, src.handle, _ptr(h_src_table), dst.handle,
                                               _ptr(h_dst_table), n, ctypes.byref(x) if x else None, flag, flag_val,
                                               _ptr(h_done), _stream(stream)), "kvx_handoff_host")
+
+
+    def handoff_batch(self, src: Pool, dst: Pool, requests, xf: Optional[Xform] = None, stream=None) -> None:
+        """Several requests between the same two pools in one launch (kvx_handoff_batch).  `requests` is a
+        sequence of (h_src_ids, h_dst_ids, flag, flag_val, h_done): int32 numpy arrays (or None for an empty
+        request), a device/peer flag address or None, the value, a pinned host word (tensor / address) or None."""
+        import numpy as np
+
+        keep, arr = [], (BatchItem * len(requests))()
+        for k, (s_ids, d_ids, flag, val, h_done) in enumerate(requests):
+            n = 0 if d_ids is None else len(d_ids)
+            if n:
+                s_ids = np.ascontiguousarray(s_ids, dtype=np.int32)
+                d_ids = np.ascontiguousarray(d_ids, dtype=np.int32)
+                if len(s_ids) != n:
+                    raise ValueError("a batched request needs equally long block-id lists")
+                keep += [s_ids, d_ids]
+            arr[k] = BatchItem(_ptr(s_ids) if n else None, _ptr(d_ids) if n else None, n, 0, flag, int(val), _ptr(h_done))
+        x = xf.c() if xf else None
+        self._check(self.lib.kvx_handoff_batch(self.handle, src.handle, dst.handle, arr, len(requests),
+                                               ctypes.byref(x) if x else None, _stream(stream)), "kvx_handoff_batch")
 
 
 STATIC_MAX_BLOCKS = 4096

@@ -171,6 +171,20 @@ class DecodeWorker(_Worker):
         self._move(rem.pool, remote_ids, self.pool, local_ids, len(local_ids), xf, flag, value, host_tables, h_done, stream)
 
 
+    def pull_many(self, key: int, requests, *, edge: Optional[TPEdge] = None, stream=None) -> None:
+        """All the requests a scheduler step has to receive from one prefill worker, in one launch
+        (= the loop over reqs_to_recv in vllm v1/nixl/worker.py:1933-1968).  `requests` is a sequence of
+        (remote_ids, local_ids, notify_slot or None, value, h_done or None); every request's release flag
+        and completion word are written when the whole batch has landed."""
+        rem = self.remotes[key]
+        xf = edge.xform(self.layout) if edge else None
+        items = []
+        for remote_ids, local_ids, slot, value, h_done in requests:
+            r, l = align_tables(np.asarray(remote_ids, np.int32), np.asarray(local_ids, np.int32))
+            items.append((r, l, rem.flag_addr(slot) if slot is not None else None, value, h_done))
+        self.ctx.handoff_batch(rem.pool, self.pool, items, xf, stream)
+
+
 class PrefillWorker(_Worker):
     """Producer (--is-prefill-worker): owns the P-side pool, publishes a finished request's block ids
     and frees them once every consumer has released them.  `push` is the write-direction variant of

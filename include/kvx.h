@@ -204,6 +204,30 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
                          void* stream);
 
 /*
+ * Several requests between the same two pools in ONE launch: what a decode worker does once per
+ * scheduler step for every request it has to receive ([vllm] start_load_kv → _read_blocks_for_req for
+ * each entry of reqs_to_recv, worker.py:1933-1968).  Short prompts are launch-bound (a handoff of 8
+ * blocks costs ~15 us, of which ~9 are launch, pipeline fill and the completion flag), so batching
+ * them pays.  Every item's `flag` (device or peer memory, may be NULL) and `h_done` (PINNED host
+ * memory, may be NULL) receive that item's flag_val once every byte of the WHOLE batch has landed.
+ * Items with n == 0 only notify.  Both pools must use the same block size.  When the ids and
+ * notifications of the batch do not fit one kernel parameter block (8000 int32 entries: the ids of
+ * both sides plus 4 per notification), or an h_done is pageable, the call degrades to one
+ * kvx_handoff_host per item — same bytes, same notifications, more launches.
+ */
+typedef struct kvx_batch_item {
+  const int32_t* h_src_table; /* host block ids on the source pool      */
+  const int32_t* h_dst_table; /* host block ids on the destination pool */
+  uint32_t n;                 /* blocks of this request                 */
+  uint32_t reserved;
+  uint64_t* flag;             /* completion flag in device / peer memory, or NULL */
+  uint64_t flag_val;
+  uint64_t* h_done;           /* completion word in pinned host memory, or NULL   */
+} kvx_batch_item;
+int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, const kvx_batch_item* items,
+                          uint32_t count, const kvx_xform* xf, void* stream);
+
+/*
  * kvx_handoff_static — the fused handoff for callers that must not allocate.  It has no
  * counterpart in the reference or in the transfer agent its images use; it exists because some
  * users of this library cannot call cudaMalloc on the request path:

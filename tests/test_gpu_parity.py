@@ -518,3 +518,48 @@ def test_mla_latent_pools(cfg_ctx, N):
     s3 = src.buf.view(np.uint16).reshape(L, nb, N * Dl)
     d3 = ddst.bytes().view(np.uint16).reshape(L, nb + 1, N * Dl)
     assert np.array_equal(d3[:, td], s3[:, ts])          # with one head NHD and HND are the same bytes
+
+
+@pytest.mark.parametrize("mode", ["one_launch", "upload_fallback", "oversize_fallback", "pageable_fallback"])
+def test_batched_requests(mode):
+    """kvx_handoff_batch: several requests (one of them empty) between the same pools, each with its own
+    release flag and pinned completion word, in one launch — and the same through every fallback."""
+    opts = dict(param_tables=0) if mode == "upload_fallback" else {}
+    c = kvx.Context(0, **opts)
+    counts = [7, 0, 33, 1, 120] if mode != "oversize_fallback" else [7, 0, 2100, 1, 2100]
+    nb = sum(counts) + 9
+    src = o.make_pool(2, 8, 64, nb, o.HND, seed=3)
+    dst = o.make_pool(2, 8, 64, nb + 5, o.NHD, fill="canary")
+    ps = o.make_table(nb, sum(counts), 1)
+    pd = o.make_table(nb + 5, sum(counts), 2)
+    dsrc, ddst = DevPool(c, src), DevPool(c, dst)
+    flags, _ = c.flags()
+    pinned = torch.zeros(len(counts), dtype=torch.int64).pin_memory()
+    pageable = np.zeros(len(counts), dtype=np.int64)
+    reqs, at = [], 0
+    for k, n in enumerate(counts):
+        c.flag_reset(flags + 8 * (20 + k), 0)
+        s_ids, d_ids = (ps[at:at + n], pd[at:at + n]) if n else (None, None)
+        done = pageable[k:k + 1] if (mode == "pageable_fallback" and k == 2) else pinned[k:k + 1]
+        reqs.append((s_ids, d_ids, flags + 8 * (20 + k) if k != 3 else None, 100 + k, done if k != 0 else None))
+        at += n
+    torch.cuda.synchronize()
+    l0 = c.launch_count
+    c.handoff_batch(dsrc.kp, ddst.kp, reqs)
+    torch.cuda.synchronize()
+    launches = c.launch_count - l0
+    assert launches == (1 if mode == "one_launch" else sum(1 for n in counts if n))
+    o.handoff(src, ps, dst, pd)
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    for k in range(len(counts)):
+        if k != 3:
+            assert c.flag_poll(flags + 8 * (20 + k), 100 + k)
+        want = 0 if k == 0 else 100 + k
+        got = pageable[k] if (mode == "pageable_fallback" and k == 2) else int(pinned[k])
+        assert got == want, (k, got)
+    bad = [(np.array([1], np.int32), np.array([nb + 5], np.int32), None, 1, None)] * 2
+    with pytest.raises(kvx.KvxError) as e:
+        c.handoff_batch(dsrc.kp, ddst.kp, bad)
+    assert e.value.code == kvx.api.ERANGE
+    c.check()
+    c.close()
