@@ -381,6 +381,34 @@ def run_single(args):
         sweep[str(s_isl)] = {"ms": round(t, 4), "payload_GBps": round(b / (t / 1e3) / 1e9, 1),
                              "hbm_frac_measured": round(2 * b / (t / 1e3) / 1e9 / hbm_peak, 4)}
 
+    # the host-table entry at the short end (launch-bound): per request, and 16 requests in one batch
+    short = {}
+    for s_isl in (128, 1024):
+        m = shape.blocks_for(s_isl)
+        R = 16
+        ids = [(np.ascontiguousarray(perm_p[j * m:(j + 1) * m]), np.ascontiguousarray(perm_d[j * m:(j + 1) * m])) for j in range(R)]
+        words = torch.zeros(R, dtype=torch.int64).pin_memory()
+        reqs = [(a, b, None, 1, words[j:j + 1]) for j, (a, b) in enumerate(ids)]
+
+        def one_by_one(_k):
+            for j, (a, b) in enumerate(ids):
+                ctx.handoff_host(P.pool, a, D.pool, b, m, None, None, 1, words[j:j + 1], stream)
+
+        def batched(_k):
+            ctx.handoff_batch(P.pool, D.pool, reqs, None, stream)
+
+        rec = {"requests": R, "payload_MiB": round(R * m * shape.regions * shape.chunk_bytes() / 2**20, 1)}
+        for name, fn in (("kvx_handoff_host_each_us", one_by_one), ("kvx_handoff_batch_us", batched)):
+            for k in range(3):
+                fn(k)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for k in range(10):
+                fn(k)
+            torch.cuda.synchronize()
+            rec[name] = round(1e5 * (time.perf_counter() - t0), 1)
+        short[str(s_isl)] = rec
+
     threads = len(os.sched_getaffinity(0))
     baselines = library_baselines(torch, np, ctx, shape, P, D, perm_p, perm_d, n, nb, payload, stream, threads)
     cpu_gbps, cpu_reps, _, _ = cpu_handoff_rate(shape, isl, min_seconds=10.0, max_reps=200, threads=threads)
@@ -408,7 +436,7 @@ def run_single(args):
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
                                    "oracle/kvx_oracle.c memcpy-per-row HND->NHD"},
         "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-        "kernels": parts, "isl_sweep": sweep, "baselines": baselines,
+        "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "baselines": baselines,
         "options": {k: ctx.get_option(k) for k in kvx.OPT},
     }
     print(json.dumps(line))
