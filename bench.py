@@ -409,6 +409,28 @@ def run_single(args):
             rec[name] = round(1e5 * (time.perf_counter() - t0), 1)
         short[str(s_isl)] = rec
 
+    # chunks of TP shards (Llama-3.1-70B, 80 layers, ISL 8192): 4, 2 and 1 KV heads per rank = 16, 8 and 4 KiB
+    # chunks; small pieces switch the launch geometry (few consumer warps, more CTAs)
+    shards = {}
+    s70 = kvx.KV_SHAPES["meta-llama/Llama-3.1-70B"]
+    for heads in (4, 2, 1):
+        m = s70.blocks_for(8192)
+        nbs = 2 * m + 1
+        Ps = synth.alloc_pool(ctx, s70, nbs, kvx.HND, heads=heads)
+        Ds = synth.alloc_pool(ctx, s70, nbs, kvx.NHD, heads=heads)
+        tp_, td_ = synth.make_table(nbs, 2 * m, 31), synth.make_table(nbs, 2 * m, 32)
+        tabs = [(torch.from_numpy(np.ascontiguousarray(tp_[j * m:(j + 1) * m])).cuda(),
+                 torch.from_numpy(np.ascontiguousarray(td_[j * m:(j + 1) * m])).cuda()) for j in range(2)]
+        f = lambda k: ctx.handoff_fused(Ps.pool, tabs[k % 2][0], Ds.pool, tabs[k % 2][1], m, None, None, 0, stream)
+        for k in range(3):
+            f(k)
+        torch.cuda.synchronize()
+        t = timed_loop(torch, stream, f, 10) / 10
+        b = m * s70.regions * s70.block_tokens * heads * s70.head_dim * s70.elem_bytes
+        shards[f"{heads}_heads_{b // (m * s70.regions) // 1024}KiB_chunks"] = {
+            "ms": round(t, 4), "hbm_GBps": round(2 * b / (t / 1e3) / 1e9, 1), "frac_measured": round(2 * b / (t / 1e3) / 1e9 / hbm_peak, 4)}
+        Ps.free(); Ds.free()
+
     threads = len(os.sched_getaffinity(0))
     baselines = library_baselines(torch, np, ctx, shape, P, D, perm_p, perm_d, n, nb, payload, stream, threads)
     cpu_gbps, cpu_reps, _, _ = cpu_handoff_rate(shape, isl, min_seconds=10.0, max_reps=200, threads=threads)
@@ -436,7 +458,7 @@ def run_single(args):
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
                                    "oracle/kvx_oracle.c memcpy-per-row HND->NHD"},
         "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-        "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "baselines": baselines,
+        "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "tp_shard_chunks": shards, "baselines": baselines,
         "options": {k: ctx.get_option(k) for k in kvx.OPT},
     }
     print(json.dumps(line))

@@ -315,10 +315,12 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   uint32_t stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
   uint32_t cons_warps = static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]);
   uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
-  const bool auto_stages = stages == 0, auto_stage_bytes = stage_bytes == 0;
+  const bool auto_stages = stages == 0, auto_stage_bytes = stage_bytes == 0, auto_cps = ctas_per_sm == 0,
+             auto_warps = cons_warps == 0;
   if (stage_bytes == 0) stage_bytes = remote ? 32768u : 16384u;
   if (stages == 0) stages = remote ? 6u : 4u;
   if (ctas_per_sm == 0) ctas_per_sm = remote ? 1u : 2u;
+  if (cons_warps == 0) cons_warps = 16u;
   const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
   int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);
   const bool pdl = ctx->opt[KVX_OPT_PDL] != 0;
@@ -382,12 +384,15 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.s_runs = pl.s_runs; p.s_run_bytes = pl.s_run_bytes; p.s_stride = pl.s_stride;
   p.d_runs = pl.d_runs; p.d_run_bytes = pl.d_run_bytes; p.d_n1 = pl.d_n1;
   p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
-  // small pieces (TP shards) keep fewer bytes per stage in flight: shrink the stages to the piece and
-  // deepen the ring within the same shared-memory budget
-  if (remote && auto_stages && auto_stage_bytes && engine == kEngineTma && pl.piece_bytes * 2u <= stage_bytes) {
-    const uint32_t budget = stages * stage_bytes;
-    stage_bytes = (pl.piece_bytes + 1023u) / 1024u * 1024u;
-    stages = std::min<uint32_t>(static_cast<uint32_t>(kvx::kMaxStages), budget / stage_bytes);
+  // Small pieces (chunks of TP shards: 8 KiB at 2 heads, 4 KiB at 1): the cost of an item is then the
+  // hand-shake between the producer and every consumer warp, not its bytes, so few fat consumer warps
+  // and more CTAs win (build/ab sweeps: 8 KiB chunks 4.9 -> 5.9 TB/s, 4 KiB chunks 2.7 -> 6.0 TB/s on
+  // one GPU); over NVLink the ring is deepened instead so that the same bytes stay in flight.
+  if (engine == kEngineTma && !ls.copy_mode && pl.piece_bytes <= 8192u && auto_stages && auto_stage_bytes) {
+    stage_bytes = 8192u;
+    stages = remote ? 8u : 4u;
+    if (auto_cps) ctas_per_sm = 3u;
+    if (auto_warps) cons_warps = 4u;
   }
   p.stages = stages; p.stage_bytes = stage_bytes;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
@@ -720,7 +725,7 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->opt[KVX_OPT_CTAS_PER_SM] = env_or("KVX_CTAS_PER_SM", 0);
   ctx->opt[KVX_OPT_STORE_MODE] = env_or("KVX_STORE_MODE", 0);
   ctx->opt[KVX_OPT_VEC_BYTES] = env_or("KVX_VEC_BYTES", 0);
-  ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 16);
+  ctx->opt[KVX_OPT_CONSUMER_WARPS] = env_or("KVX_CONSUMER_WARPS", 0);
   ctx->opt[KVX_OPT_L2_HINT] = env_or("KVX_L2_HINT", 0);
   ctx->opt[KVX_OPT_PDL] = env_or("KVX_PDL", 1);
   ctx->opt[KVX_OPT_PARAM_TABLES] = env_or("KVX_PARAM_TABLES", 8000);
@@ -757,7 +762,7 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
     case KVX_OPT_CTAS_PER_SM: if (value < 0 || value > 32) return KVX_EINVAL; break;
     case KVX_OPT_STORE_MODE: if (value < 0 || value > 2) return KVX_EINVAL; break;
     case KVX_OPT_VEC_BYTES: if (value != 0 && value != 16 && value != 32) return KVX_EINVAL; break;
-    case KVX_OPT_CONSUMER_WARPS: if (value < 1 || value > 16) return KVX_EINVAL; break;
+    case KVX_OPT_CONSUMER_WARPS: if (value < 0 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PDL: if (value < 0 || value > 1) return KVX_EINVAL; break;
     case KVX_OPT_PARAM_TABLES: if (value < 0 || value > kParamTabMax) return KVX_EINVAL; break;

@@ -55,7 +55,8 @@ enum {
   KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this; 0 (default) = 2 on-GPU, 1 over NVLink */
   KVX_OPT_STORE_MODE = 4,  /* tma: 0 auto, 1 thread stores, 2 bulk stores                    */
   KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
-  KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16)                          */
+  KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16); 0 (default) = 16, or 4 when a
+                                 piece is 8 KiB or less (chunks of TP shards)                    */
   KVX_OPT_L2_HINT = 7,     /* 1: evict_first on loads                                        */
   KVX_OPT_PDL = 8,         /* 1 (default): programmatic dependent launch — a transfer kernel may
                               become resident while the previous kernel on the stream drains; it
