@@ -337,6 +337,7 @@ def run_single(args):
     stage = torch.empty(payload, dtype=torch.uint8, device="cuda")
     stage2 = torch.empty(payload, dtype=torch.uint8, device="cuda")
     xf = kvx.Xform(0, 0, 0, kvx.NHD)
+    D2 = synth.alloc_pool(ctx, shape, nb, kvx.HND)   # identity control: HND prefill pool -> HND decode pool
     asc = [torch.arange(1 + j * n, 1 + (j + 1) * n, dtype=torch.int32, device="cuda") for j in range(sets)]
     parts = {}
     reps = max(3, min(args.steps, 10))
@@ -344,7 +345,7 @@ def run_single(args):
         ("gather_hnd_to_nhd", lambda k: ctx.gather(P.pool, d_src[k % sets], n, stage, xf, stream)),
         ("copy_local", lambda k: ctx.copy(stage, stage2, payload, None, 0, stream)),
         ("scatter_nhd", lambda k: ctx.scatter(stage2, D.pool, d_dst[k % sets], n, xf, stream)),
-        ("fused_identity_hnd", lambda k: ctx.handoff_fused(P.pool, d_src[k % sets], P.pool, d_dst[(k + 1) % sets], n, None, None, 0, stream)),
+        ("fused_identity_hnd", lambda k: ctx.handoff_fused(P.pool, d_src[k % sets], D2.pool, d_dst[k % sets], n, None, None, 0, stream)),
         # best-case control: contiguous ascending block ids on both sides
         ("fused_hnd_to_nhd_contiguous_tables", lambda k: ctx.handoff_fused(P.pool, asc[k % sets], D.pool, asc[(k + 1) % sets], n, None, None, 0, stream)),
     ):
@@ -362,6 +363,7 @@ def run_single(args):
     t = timed_loop(torch, stream, lambda k: stage2.copy_(stage), reps) / reps
     parts["torch_copy_same_bytes"] = {"ms": round(t, 4), "hbm_GBps": round(2 * payload / (t / 1e3) / 1e9, 1)}
     del stage, stage2
+    D2.free()
 
     # ISL sweep of config #2 (fused, HND→NHD)
     sweep = {}

@@ -307,7 +307,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
 
   int engine = static_cast<int>(ctx->opt[KVX_OPT_ENGINE]);
   // Pipeline geometry, 0 = choose here.  A transfer whose bytes stay on this GPU is HBM-bound and wants
-  // every SM: 4 x 16 KiB stages, two CTAs per SM (profiles/r01_sweep_*).  A transfer with one side in a
+  // every SM: 4 x 16 KiB stages (profiles/r01_sweep_*).  A transfer with one side in a
   // peer's memory is NVLink-bound: ~6 MiB in flight saturate the link (tools/footprint.py), so it runs
   // deep pipelines (6 x 32 KiB) in few CTAs and leaves most SMs to the decode steps beside it.
   const bool remote = ls.src_is_peer || ls.dst_is_peer_known;
@@ -319,7 +319,11 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
              auto_warps = cons_warps == 0;
   if (stage_bytes == 0) stage_bytes = remote ? 32768u : 16384u;
   if (stages == 0) stages = remote ? 6u : 4u;
-  if (ctas_per_sm == 0) ctas_per_sm = remote ? 1u : 2u;
+  // One CTA per SM: with dependent launch the next handoff's CTA then fits beside the draining one
+  // (2 x 64 KiB, 2 x 544 threads) and its set-up and pipeline fill overlap the tail completely
+  // (build/ab sweep after PDL: 15.5 -> 11.6 us at 8 blocks, 47.3 -> 44.1 at 64, 296.6 -> 294.1 at 512).
+  // The register engine has no shared-memory ring to keep bytes in flight and keeps two.
+  if (ctas_per_sm == 0) ctas_per_sm = (static_cast<int>(ctx->opt[KVX_OPT_ENGINE]) == kEngineLdg) ? 2u : 1u;
   if (cons_warps == 0) cons_warps = 16u;
   const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
   int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);

@@ -52,7 +52,8 @@ enum {
                               on this GPU, 6..8 when one side is a peer's memory               */
   KVX_OPT_STAGE_BYTES = 2, /* tma: bytes per stage (multiple of 1024); 0 (default) = 16 KiB
                               on-GPU, 32 KiB over NVLink                                       */
-  KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this; 0 (default) = 2 on-GPU, 1 over NVLink */
+  KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this; 0 (default) = 1 (3 for pieces of 8 KiB or
+                              less, 2 for the register engine)                                 */
   KVX_OPT_STORE_MODE = 4,  /* tma: 0 auto, 1 thread stores, 2 bulk stores                    */
   KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
   KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16); 0 (default) = 16, or 4 when a
