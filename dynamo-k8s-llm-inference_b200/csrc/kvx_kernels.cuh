@@ -367,6 +367,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
     grid_dep_wait();
     RawItem raw{};
     if (lane < my_items) item_load(p, tab, bid + lane * grid, raw);
+    unsigned s = 0, phase = 0;  // ring position and its parity, advanced by hand: no division per item
     for (unsigned base = 0; base < my_items; base += 32u) {
       unsigned long long sa = 0, da = 0;
       unsigned bytes = 0;
@@ -378,10 +379,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
         const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
         const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
         const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
-        const unsigned it = base + j;
-        const unsigned s = it % S;
-        const unsigned round = it / S;
-        mbar_wait(&empty_bar[s], (round & 1u) ^ 1u);
+        mbar_wait(&empty_bar[s], phase ^ 1u);
         unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
         if (lane == 0) {
           meta_dst[s] = dst;
@@ -406,6 +404,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
             }
           }
         }
+        if (++s == S) { s = 0; phase ^= 1u; }
       }
     }
   } else {
@@ -418,9 +417,9 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
       unsigned prev_stage = 0;
       bool have_prev = false;
       grid_dep_wait();
+      unsigned s = 0, phase = 0;
       for (unsigned it = 0; it < my_items; ++it) {
-        const unsigned s = it % S;
-        mbar_wait(&full_bar[s], (it / S) & 1u);
+        mbar_wait(&full_bar[s], phase);
         const unsigned long long dst = meta_dst[s];
         const unsigned nbytes = meta_bytes[s];
         const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
@@ -440,6 +439,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
         }
         prev_stage = s;
         have_prev = true;
+        if (++s == S) { s = 0; phase ^= 1u; }
       }
       bulk_wait<0>();  // all bytes written before the completion fence
     } else {
@@ -454,9 +454,9 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
         doff[k] = dst_run_offset(p, x) + (u % upr) * VEC;
       }
       grid_dep_wait();
+      unsigned s = 0, phase = 0;
       for (unsigned it = 0; it < my_items; ++it) {
-        const unsigned s = it % S;
-        mbar_wait(&full_bar[s], (it / S) & 1u);
+        mbar_wait(&full_bar[s], phase);
         const unsigned long long dst = meta_dst[s];
         const unsigned units = meta_bytes[s] / VEC;
         const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
@@ -473,6 +473,7 @@ __device__ __forceinline__ void xfer_tma_body(const XferParams& p, const Tab tab
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty_bar[s]);
+        if (++s == S) { s = 0; phase ^= 1u; }
       }
     }
   }
