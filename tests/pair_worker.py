@@ -111,6 +111,39 @@ def main():
         assert np.array_equal(w.kv.to_numpy(), want.buf), "push: bytes on the decode GPU differ from the oracle"
         print("pair ok")
     dist.barrier()
+
+    # 3) a scheduler step's worth of requests in one launch: three requests (one with a prefix hit), each
+    #    releasing its prefill blocks through its own flag in the prefill worker's memory
+    counts = [5, 9, 3]
+    if rank == 0:
+        reqs_src = [alloc.allocate(f"b{k}", c) for k, c in enumerate(counts)]
+    else:
+        synth.fill_canary(w.kv)
+        reqs_dst = [alloc.allocate(f"b{k}", c - (2 if k == 1 else 0)) for k, c in enumerate(counts)]
+        torch.cuda.synchronize()
+    for k in range(3):
+        if rank == 0:
+            w.expect(10 + k)
+    torch.cuda.synchronize()
+    box = [reqs_src if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    if rank == 1:
+        words = torch.zeros(3, dtype=torch.int64).pin_memory()
+        w.pull_many(0, [(box[0][k], reqs_dst[k], 10 + k, 50 + k, words[k:k + 1]) for k in range(3)])
+        torch.cuda.synchronize()
+        w.ctx.check()
+        want3 = o.make_pool(shape.layers, 8, 64, nb_d, o.NHD, fill="canary")
+        for k in range(3):
+            s_ids, d_ids = align_tables(box[0][k], reqs_dst[k])
+            o.handoff(src_host, s_ids, want3, d_ids)
+        assert np.array_equal(w.kv.to_numpy(), want3.buf), "pull_many: bytes on the decode GPU differ from the oracle"
+        assert words.tolist() == [50, 51, 52]
+    dist.barrier()
+    if rank == 0:
+        for k in range(3):
+            assert w.poll(10 + k, 50 + k), f"request {k} was not released"
+        print("batch ok")
+    dist.barrier()
     w.close()
     dist.destroy_process_group()
 

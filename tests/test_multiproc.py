@@ -69,7 +69,7 @@ def test_two_process_handoff_over_ipc():
         pytest.skip("no GPU")
     r = _torchrun([], 29612)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert "pull ok" in r.stdout and "pair ok" in r.stdout
+    assert "pull ok" in r.stdout and "pair ok" in r.stdout and "batch ok" in r.stdout
 
 
 @pytest.mark.gpu
