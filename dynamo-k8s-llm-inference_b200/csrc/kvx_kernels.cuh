@@ -314,12 +314,20 @@ __device__ __forceinline__ void finish_and_flag(const XferParams& p, const Tab& 
       const unsigned prev = atomicAdd(p.done_counter, 1u);
       if (prev == gridDim.x - 1) {
         last = 1u;
-        if (p.flag_local) __threadfence(); else __threadfence_system();
         *p.done_counter = 0u;
-        if (p.flag != nullptr)
-          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
-        if (p.flag2 != nullptr)
-          asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p.flag2), "l"(p.flag_val) : "memory");
+        if (p.flag_local) {
+          // data and flag both live in this GPU's memory: every observer, local or remote, reads them
+          // through this GPU's L2, so one device-scope release orders them for all of them
+          asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+        } else {
+          // one system-wide fence (acquire for the other CTAs' counts, release for everything they
+          // published), then plain system-scope stores: they cannot pass the fence
+          __threadfence_system();
+          if (p.flag != nullptr)
+            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.flag), "l"(p.flag_val) : "memory");
+          if (p.flag2 != nullptr)
+            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p.flag2), "l"(p.flag_val) : "memory");
+        }
       }
     }
     if (p.notify_count != 0u) {
