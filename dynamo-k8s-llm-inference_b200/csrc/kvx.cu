@@ -321,7 +321,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (stages == 0) stages = remote ? 6u : 4u;
   // One CTA per SM: with dependent launch the next handoff's CTA then fits beside the draining one
   // (2 x 64 KiB, 2 x 544 threads) and its set-up and pipeline fill overlap the tail completely
-  // (build/ab sweep after PDL: 15.5 -> 11.6 us at 8 blocks, 47.3 -> 44.1 at 64, 296.6 -> 294.1 at 512).
+  // (tools/small_requests.py: 15.5 -> 11.6 us at 8 blocks, 47.3 -> 44.1 at 64, 296.6 -> 294.1 at 512).
   // The register engine has no shared-memory ring to keep bytes in flight and keeps two.
   if (ctas_per_sm == 0) ctas_per_sm = (static_cast<int>(ctx->opt[KVX_OPT_ENGINE]) == kEngineLdg) ? 2u : 1u;
   if (cons_warps == 0) cons_warps = 16u;
@@ -390,7 +390,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
   // Small pieces (chunks of TP shards: 8 KiB at 2 heads, 4 KiB at 1): the cost of an item is then the
   // hand-shake between the producer and every consumer warp, not its bytes, so few fat consumer warps
-  // and more CTAs win (build/ab sweeps: 8 KiB chunks 4.9 -> 5.9 TB/s, 4 KiB chunks 2.7 -> 6.0 TB/s on
+  // and more CTAs win (tools/small_pieces.py: 8 KiB chunks 4.9 -> 5.9 TB/s, 4 KiB chunks 2.7 -> 6.0 TB/s on
   // one GPU); over NVLink the ring is deepened instead so that the same bytes stay in flight.
   if (engine == kEngineTma && !ls.copy_mode && pl.piece_bytes <= 8192u && auto_stages && auto_stage_bytes) {
     stage_bytes = 8192u;
