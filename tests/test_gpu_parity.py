@@ -563,3 +563,27 @@ def test_batched_requests(mode):
     assert e.value.code == kvx.api.ERANGE
     c.check()
     c.close()
+
+
+def test_flag_wait_times_out_and_context_recovers(ctx):
+    """A transfer that never completes (the peer died) must surface as KVX_ETIMEOUT at the next check,
+    never as a hang; the context keeps working afterwards."""
+    flags, _ = ctx.flags()
+    slot = flags + 8 * 30
+    ctx.flag_reset(slot, 0)
+    torch.cuda.synchronize()
+    ctx.flag_wait(slot, 1, timeout_ms=50)      # nobody will ever write 1
+    torch.cuda.synchronize()
+    with pytest.raises(kvx.KvxError) as e:
+        ctx.check()
+    assert e.value.code == kvx.api.ETIMEOUT
+    ctx.check()                                 # the error is reported once
+    src = o.make_pool(1, 8, 64, 6, o.NHD, seed=2)
+    dst = o.make_pool(1, 8, 64, 6, o.HND, fill="canary")
+    dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
+    ctx.handoff_fused(dsrc.kp, dev_table([2, 4]), ddst.kp, dev_table([5, 1]), 2, flag=slot, flag_val=1)
+    ctx.flag_wait(slot, 1, timeout_ms=2000)     # now it arrives (same stream: already there)
+    torch.cuda.synchronize()
+    ctx.check()
+    o.handoff(src, [2, 4], dst, [5, 1])
+    assert np.array_equal(ddst.bytes(), dst.buf)
