@@ -274,6 +274,51 @@ cudaError_t launch_kernel(K kernel, uint32_t grid, uint32_t block, size_t smem, 
   return cudaLaunchKernelEx(&cfg, kernel, p);
 }
 
+// ---- launch geometry ----------------------------------------------------------------------------
+// Every KVX_OPT_* geometry value of 0 means "choose here", from what the sweeps under tools/ and
+// profiles/ measured on B200:
+//   on-GPU transfers are HBM-bound and want every SM: 4 x 16 KiB stages, 16 consumer warps, ONE CTA per
+//     SM — with dependent launch the next handoff's CTA then fits beside the draining one (2 x 64 KiB,
+//     2 x 544 threads) and its set-up and pipeline fill overlap the tail completely
+//     (tools/small_requests.py: 15.5 -> 11.6 us at 8 blocks, 47.3 -> 44.1 at 64, 296.6 -> 294.1 at 512);
+//   pieces of 8 KiB or less (chunks of TP shards: 8 KiB at 2 heads, 4 KiB at 1): an item then costs the
+//     hand-shake between the producer and every consumer warp, not its bytes, so few fat consumer warps
+//     and more CTAs win (tools/small_pieces.py: 8 KiB chunks 4.9 -> 5.9 TB/s, 4 KiB chunks 2.7 -> 6.0 TB/s);
+//   transfers with one side in a peer's memory are NVLink-bound: ~6 MiB in flight saturate the link
+//     (tools/footprint.py), so they run deep rings (6 x 32 KiB, 8 x 8 KiB for small pieces) in just
+//     enough CTAs for kNvlinkInFlightBytes and leave the other SMs to the work running beside them;
+//   the register engine has no shared-memory ring to keep bytes in flight and keeps two CTAs per SM.
+struct Geometry {
+  uint32_t stages, stage_bytes, ctas_per_sm, cons_warps, max_ctas;
+};
+
+uint32_t plan_stage_bytes(const kvx_ctx* ctx, bool remote) {
+  const uint32_t opt = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
+  return opt ? opt : (remote ? 32768u : 16384u);
+}
+
+Geometry resolve_geometry(const kvx_ctx* ctx, bool remote, int engine, bool copy_mode, uint32_t piece_bytes) {
+  Geometry g{};
+  g.stages = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGES]);
+  g.stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
+  g.ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
+  g.cons_warps = static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]);
+  const bool small = engine == kEngineTma && !copy_mode && piece_bytes <= 8192u && g.stages == 0 && g.stage_bytes == 0;
+  if (g.stage_bytes == 0) g.stage_bytes = small ? 8192u : plan_stage_bytes(ctx, remote);
+  if (g.stages == 0) g.stages = small ? (remote ? 8u : 4u) : (remote ? 6u : 4u);
+  if (g.ctas_per_sm == 0) g.ctas_per_sm = small ? 3u : (engine == kEngineLdg ? 2u : 1u);
+  if (g.cons_warps == 0) g.cons_warps = small ? 4u : 16u;
+  g.max_ctas = static_cast<uint32_t>(ctx->sms) * g.ctas_per_sm;
+  if (ctx->opt[KVX_OPT_MAX_CTAS] > 0) {  // the caller bounds the SMs a transfer occupies
+    g.max_ctas = std::min<uint32_t>(g.max_ctas, static_cast<uint32_t>(ctx->opt[KVX_OPT_MAX_CTAS]));
+  } else if (remote && engine == kEngineTma) {
+    const uint64_t in_flight_per_cta = static_cast<uint64_t>(g.stages) * piece_bytes;
+    const uint32_t need = static_cast<uint32_t>((kNvlinkInFlightBytes + in_flight_per_cta - 1) / in_flight_per_cta);
+    g.max_ctas = std::min<uint32_t>(g.max_ctas, std::max<uint32_t>(16u, need));
+  }
+  return g;
+}
+
 // The default kernel with the request's block ids copied into its parameter block: no H2D copy, no
 // copy-engine hand-over before the launch.
 template <int NT>
@@ -306,29 +351,12 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (!guard.ok) return cuda_fail(ctx, cudaGetLastError(), "cudaSetDevice");
 
   int engine = static_cast<int>(ctx->opt[KVX_OPT_ENGINE]);
-  // Pipeline geometry, 0 = choose here.  A transfer whose bytes stay on this GPU is HBM-bound and wants
-  // every SM: 4 x 16 KiB stages (profiles/r01_sweep_*).  A transfer with one side in a
-  // peer's memory is NVLink-bound: ~6 MiB in flight saturate the link (tools/footprint.py), so it runs
-  // deep pipelines (6 x 32 KiB) in few CTAs and leaves most SMs to the decode steps beside it.
-  const bool remote = ls.src_is_peer || ls.dst_is_peer_known;
-  uint32_t stages = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGES]);
-  uint32_t stage_bytes = static_cast<uint32_t>(ctx->opt[KVX_OPT_STAGE_BYTES]);
-  uint32_t cons_warps = static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]);
-  uint32_t ctas_per_sm = static_cast<uint32_t>(ctx->opt[KVX_OPT_CTAS_PER_SM]);
-  const bool auto_stages = stages == 0, auto_stage_bytes = stage_bytes == 0, auto_cps = ctas_per_sm == 0,
-             auto_warps = cons_warps == 0;
-  if (stage_bytes == 0) stage_bytes = remote ? 32768u : 16384u;
-  if (stages == 0) stages = remote ? 6u : 4u;
-  // One CTA per SM: with dependent launch the next handoff's CTA then fits beside the draining one
-  // (2 x 64 KiB, 2 x 544 threads) and its set-up and pipeline fill overlap the tail completely
-  // (tools/small_requests.py: 15.5 -> 11.6 us at 8 blocks, 47.3 -> 44.1 at 64, 296.6 -> 294.1 at 512).
-  // The register engine has no shared-memory ring to keep bytes in flight and keeps two.
-  if (ctas_per_sm == 0) ctas_per_sm = (static_cast<int>(ctx->opt[KVX_OPT_ENGINE]) == kEngineLdg) ? 2u : 1u;
-  if (cons_warps == 0) cons_warps = 16u;
+  if (engine == kEngineAuto) engine = kEngineTma;
+  const bool remote = ls.src_is_peer || ls.dst_is_peer_known;  // one side in a peer's memory: NVLink-bound
+  const uint32_t stage_cap = plan_stage_bytes(ctx, remote);     // bytes one piece may fill
   const int store_mode = static_cast<int>(ctx->opt[KVX_OPT_STORE_MODE]);
   int vec_opt = static_cast<int>(ctx->opt[KVX_OPT_VEC_BYTES]);
   const bool pdl = ctx->opt[KVX_OPT_PDL] != 0;
-  if (engine == kEngineAuto) engine = kEngineTma;
 
   constexpr uint32_t kLdgThreads = 256;
   // KMAX by vector width: 8 units of 16 B or 4 units of 32 B per thread.
@@ -341,8 +369,9 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.regions = ls.regions;
   Plan pl{};
   if (ls.copy_mode) {
-    uint32_t piece = engine == kEngineTma ? stage_bytes : ldg_cap16;
-    if (engine == kEngineTma && store_mode == 1) piece = std::min<uint32_t>(piece, cons_warps * 32u * 8u * 16u);
+    uint32_t piece = engine == kEngineTma ? stage_cap : ldg_cap16;
+    if (engine == kEngineTma && store_mode == 1 && ctx->opt[KVX_OPT_CONSUMER_WARPS] > 0)
+      piece = std::min<uint32_t>(piece, static_cast<uint32_t>(ctx->opt[KVX_OPT_CONSUMER_WARPS]) * 32u * 8u * 16u);
     const uint64_t items = (ls.copy_bytes + piece - 1) / piece;
     if (items == 0) return KVX_OK;
     if (items >= (1ull << 31)) return KVX_EUNSUPPORTED;
@@ -355,13 +384,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     const uint64_t tail = ls.copy_bytes - (items - 1) * piece;
     p.tail_bytes = tail == piece ? 0u : static_cast<uint32_t>(tail);
   } else {
-    uint32_t cap;
-    if (engine == kEngineTma) {
-      cap = stage_bytes;
-    } else {
-      cap = ldg_cap16;
-    }
-    int32_t rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, cap, &pl);
+    int32_t rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, engine == kEngineTma ? stage_cap : ldg_cap16, &pl);
     if (rc == KVX_EUNSUPPORTED && engine == kEngineTma) {  // unit larger than a stage: register path
       engine = kEngineLdg;
       rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, ldg_cap16, &pl);
@@ -388,16 +411,8 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.s_runs = pl.s_runs; p.s_run_bytes = pl.s_run_bytes; p.s_stride = pl.s_stride;
   p.d_runs = pl.d_runs; p.d_run_bytes = pl.d_run_bytes; p.d_n1 = pl.d_n1;
   p.d_stride_a = pl.d_stride_a; p.d_stride_b = pl.d_stride_b;
-  // Small pieces (chunks of TP shards: 8 KiB at 2 heads, 4 KiB at 1): the cost of an item is then the
-  // hand-shake between the producer and every consumer warp, not its bytes, so few fat consumer warps
-  // and more CTAs win (tools/small_pieces.py: 8 KiB chunks 4.9 -> 5.9 TB/s, 4 KiB chunks 2.7 -> 6.0 TB/s on
-  // one GPU); over NVLink the ring is deepened instead so that the same bytes stay in flight.
-  if (engine == kEngineTma && !ls.copy_mode && pl.piece_bytes <= 8192u && auto_stages && auto_stage_bytes) {
-    stage_bytes = 8192u;
-    stages = remote ? 8u : 4u;
-    if (auto_cps) ctas_per_sm = 3u;
-    if (auto_warps) cons_warps = 4u;
-  }
+  const Geometry g = resolve_geometry(ctx, remote, engine, ls.copy_mode, pl.piece_bytes);
+  const uint32_t stages = g.stages, stage_bytes = g.stage_bytes, cons_warps = g.cons_warps;
   p.stages = stages; p.stage_bytes = stage_bytes;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
   p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
@@ -419,16 +434,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (vec_opt == 0) vec_opt = 16;  // measured: 16-byte stores beat 32-byte ones on B200 for this path
   if (vec_opt == 32 && !ok32) vec_opt = 16;
 
-  uint32_t max_ctas = static_cast<uint32_t>(ctx->sms) * ctas_per_sm;
-  // A serving engine that runs decode steps next to the handoff bounds the SMs the transfer occupies.
-  if (ctx->opt[KVX_OPT_MAX_CTAS] > 0) {
-    max_ctas = std::min<uint32_t>(max_ctas, static_cast<uint32_t>(ctx->opt[KVX_OPT_MAX_CTAS]));
-  } else if (remote && engine == kEngineTma) {
-    const uint64_t in_flight_per_cta = static_cast<uint64_t>(stages) * pl.piece_bytes;
-    const uint32_t need = static_cast<uint32_t>((kNvlinkInFlightBytes + in_flight_per_cta - 1) / in_flight_per_cta);
-    max_ctas = std::min<uint32_t>(max_ctas, std::max<uint32_t>(16u, need));
-  }
-  const uint32_t grid = std::min<uint32_t>(max_ctas, p.total_items);
+  const uint32_t grid = std::min<uint32_t>(g.max_ctas, p.total_items);
 
   if (ls.h_src_tab != nullptr) {
     // Host tables ride in the parameters only with the default kernel (TMA engine, 16-byte thread stores).
@@ -438,13 +444,9 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   }
 
   if (engine == kEngineTma) {
-    const bool dst_single_run = pl.d_runs == 1;
-    int mode = store_mode;  // 1 thread stores, 2 bulk stores
-    // measured (profiles/r01_sweep.md): thread stores match or beat bulk stores at the default stage size
-    if (mode == 0) mode = 1;
-    (void)dst_single_run;
+    // store_mode 0 = thread stores: they match or beat bulk stores at these stage sizes (profiles/r01_sweep_*)
     const size_t smem = static_cast<size_t>(stages) * stage_bytes;
-    if (mode == 2) {
+    if (store_mode == 2) {
       if (stages < 2) return KVX_EINVAL;
       auto k = kvx::kvx_xfer_tma_kernel<0, 1>;
       int32_t rc = set_smem(ctx, k, smem);
