@@ -2,8 +2,9 @@
 
   -u <api-url> -m <model> -o <output-dir> -b <benchmark-name> [-p] [-h]
 
-Same required flags, same messages, same exit codes.  `-u` is a transport URL instead of an HTTP
-endpoint:  kvx://local?manifest=<DynamoGraphDeployment yaml>[&isl=8192][&requests=64][&concurrency=1]
+Same required flags, same messages, same exit codes.  `-u` is either an OpenAI-compatible HTTP endpoint, as
+in the reference (driven by kvx/httpload.py with the shape of the reference's multi_convos_parallel.sh), or a
+transport URL:  kvx://local?manifest=<DynamoGraphDeployment yaml>[&isl=8192][&requests=64][&concurrency=1]
            kvx://local?prefill=4&decode=4[&ptp=4&dtp=2][&isl=1024,2048,...][&layout=nhd][&route=spread]
 Results land under <output-dir>/<benchmark-name>/results.json; -p adds SVG plots from that tree.
 """
@@ -102,6 +103,14 @@ def main(argv: Optional[List[str]] = None) -> int:
     if parsed is None:
         return rc
     url, model, out_dir, name, plots = parsed
+    if urlparse(url).scheme in ("http", "https"):
+        # the reference's own usage: an OpenAI-compatible endpoint (the Frontend pod, or `python -m kvx.frontend`)
+        from .httpload import run_http_benchmark
+
+        os.makedirs(out_dir, exist_ok=True)
+        summary = run_http_benchmark(url, model, os.path.join(out_dir, name))
+        print(json.dumps(summary))
+        return 1 if (summary["failed_conversations"] or not summary["requests"]) else 0
     try:
         topo, cfg = build_job(url, model)
     except (ValueError, OSError) as e:

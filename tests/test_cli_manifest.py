@@ -39,8 +39,8 @@ spec:
 """
 
 
-def _run(*args):
-    return subprocess.run([RUNNER, *args], capture_output=True, text=True)
+def _run(*args, env=None):
+    return subprocess.run([RUNNER, *args], capture_output=True, text=True, env=dict(os.environ, **(env or {})))
 
 
 def test_usage_and_exit_codes_match_reference_runner():
@@ -58,8 +58,11 @@ def test_usage_and_exit_codes_match_reference_runner():
 
 
 def test_bad_endpoint_and_model_fail_cleanly(tmp_path):
-    r = _run("-u", "http://10.0.0.1:30080", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "x")
+    r = _run("-u", "ftp://10.0.0.1:30080", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "x")
     assert r.returncode == 1 and "unsupported endpoint scheme" in r.stderr
+    # an HTTP endpoint nobody listens on: every conversation fails, the runner exits 1 (no hang)
+    r = _run("-u", "http://127.0.0.1:1", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "dead", env={"NUM_CONVOS": "2"})
+    assert r.returncode == 1 and '"failed_conversations": [1, 2]' in r.stdout
     r = _run("-u", "kvx://local", "-m", "no/such-model", "-o", str(tmp_path), "-b", "x")
     assert r.returncode == 1 and "unknown model" in r.stderr
 

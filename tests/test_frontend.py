@@ -111,3 +111,55 @@ def test_frontend_runs_real_handoffs():
     finally:
         srv.shutdown()
         be.close()
+
+
+def test_runner_drives_an_http_endpoint(server, tmp_path, monkeypatch):
+    """run-benchmarks.sh -u http://... : bounded-concurrency three-turn conversations against the endpoint,
+    results under <out>/<name>/results.json, exit 1 when any conversation fails (as the reference's script)."""
+    import os
+
+    from kvx import cli
+
+    base, be = server
+    monkeypatch.setenv("NUM_CONVOS", "4")
+    monkeypatch.setenv("CONCURRENCY", "2")
+    monkeypatch.setenv("KVX_PROMPT_TOKENS", "64")
+    rc = cli.main(["-u", base + "/v1/chat/completions", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "http1"])
+    assert rc == 0
+    res = json.load(open(os.path.join(tmp_path, "http1", "results.json")))
+    s = res["summary"]
+    assert s["requests"] == 12 and not s["failed_conversations"] and len(be.calls) == 12
+    assert s["kv_transfer"]["requests"] == 12 and s["time_to_first_token_seconds"]["p50"] > 0
+    prompts = [r["prompt_tokens"] for r in res["requests"] if r["conversation"] == 1]
+    assert prompts == sorted(prompts) and prompts[0] < prompts[-1]      # the conversation grows turn by turn
+    # a wrong model name is an error object on every first turn: the run fails
+    rc = cli.main(["-u", base, "-m", "meta-llama/Llama-3.1-8B", "-o", str(tmp_path), "-b", "http2"])
+    assert rc == 1
+    assert len(json.load(open(os.path.join(tmp_path, "http2", "results.json")))["summary"]["failed_conversations"]) == 4
+
+
+@pytest.mark.gpu
+def test_runner_against_real_frontend(tmp_path, monkeypatch):
+    """The whole chain the reference describes, on one box: runner (-u http://...) -> Frontend stand-in ->
+    prefill/decode workers -> a real KV handoff per request."""
+    import os
+
+    import kvx
+    from kvx import cli
+    from kvx.frontend import InProcessHandoff
+
+    be = InProcessHandoff(kvx.KV_SHAPES["Qwen/Qwen3-0.6B"], max_isl=8192)
+    srv = Frontend("Qwen/Qwen3-0.6B", be).serve("127.0.0.1", 0)
+    monkeypatch.setenv("NUM_CONVOS", "6")
+    monkeypatch.setenv("CONCURRENCY", "3")
+    monkeypatch.setenv("KVX_PROMPT_TOKENS", "2048")
+    try:
+        rc = cli.main(["-u", f"http://127.0.0.1:{srv.server_address[1]}", "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "chain"])
+        assert rc == 0
+        s = json.load(open(os.path.join(tmp_path, "chain", "results.json")))["summary"]
+        assert s["requests"] == 18 and not s["failed_conversations"]
+        assert s["kv_transfer"]["bytes_transferred"] > 18 * 128 * 56 * 32768 and s["kv_transfer"]["throughput_GBps"] > 100
+        assert be.p.blocks.free_blocks == be.d.blocks.free_blocks
+    finally:
+        srv.shutdown()
+        be.close()
