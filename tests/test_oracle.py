@@ -222,3 +222,55 @@ def test_property_numpy_equals_c(L, H, D, N, n, ls, ld, so, do, hc, seed):
     o.handoff(src, ts, d1, td, xf)
     assert oc.handoff(src, ts, d2, td, xf, threads=2) == 0
     assert np.array_equal(d1.buf, d2.buf)
+
+
+def test_torch_cpu_twin_agrees_with_numpy_oracle():
+    """A second, independent restatement: the receive path the reference's images run today —
+    land the raw blocks, then index_select -> permute -> index_copy_ per region on torch.bfloat16 tensors
+    ([vllm] kv_connector/utils.py:255-277) — against the NumPy oracle on random bit patterns (NaN / Inf /
+    denormal bf16 included), TP head slot included.  Equality is on the integer views."""
+    import torch
+
+    L, H, N, D, nb_p, nb_d, n = 2, 8, 16, 64, 23, 29, 17
+    src = o.make_pool(L, H, D, nb_p, o.HND, seed=91)
+    dst = o.make_pool(L, H, D, nb_d, o.NHD, fill="canary")
+    ts, td = o.make_table(nb_p, n, 1), o.make_table(nb_d, n, 2)
+    o.handoff(src, ts, dst, td)
+    p = torch.from_numpy(src.buf.copy()).view(torch.bfloat16).view(2 * L, nb_p, H, N, D)            # HND pools
+    d = torch.from_numpy(o.make_pool(L, H, D, nb_d, o.NHD, fill="canary").buf).view(torch.bfloat16).view(2 * L, nb_d, N, H, D)
+    si, di = torch.from_numpy(ts.astype(np.int64)), torch.from_numpy(td.astype(np.int64))
+    for r in range(2 * L):
+        blocks = p[r].index_select(0, si)                       # [n, H, N, D]
+        d[r].index_copy_(0, di, blocks.permute(0, 2, 1, 3).contiguous())
+    assert np.array_equal(d.contiguous().view(torch.int16).numpy().view(np.uint8).reshape(-1), dst.buf)
+    # TP4 -> TP2 on the decode side: two 2-head sources land in head slots 0 and 2 of a 4-head NHD chunk
+    srcs = [o.make_pool(L, 2, D, nb_p, o.HND, seed=5 + r) for r in range(2)]
+    dst2 = o.make_pool(L, 4, D, nb_d, o.NHD, fill="canary")
+    d2 = torch.from_numpy(dst2.buf.copy()).view(torch.bfloat16).view(2 * L, nb_d, N, 4, D)
+    for s, pool in enumerate(srcs):
+        o.handoff(pool, ts, dst2, td, o.Xform(0, 2 * s, 2))
+        ps = torch.from_numpy(pool.buf.copy()).view(torch.bfloat16).view(2 * L, nb_p, 2, N, D)
+        for r in range(2 * L):
+            got = d2[r].index_select(0, di)
+            got[:, :, 2 * s:2 * s + 2] = ps[r].index_select(0, si).permute(0, 2, 1, 3)
+            d2[r].index_copy_(0, di, got)
+    assert np.array_equal(d2.contiguous().view(torch.int16).numpy().view(np.uint8).reshape(-1), dst2.buf)
+
+
+@pytest.mark.skipif(not os.environ.get("KVX_TEST_VLLM"), reason="set KVX_TEST_VLLM=1 to import the on-box vLLM (about 30 s)")
+def test_live_vllm_helper_agrees_with_oracle():
+    """The helper the golden fixtures were generated from, called live (only where vLLM is installed)."""
+    torch = pytest.importorskip("torch")
+    utils = pytest.importorskip("vllm.distributed.kv_transfer.kv_connector.utils")
+    L, H, N, D, nb_p, nb_d, n = 1, 4, 16, 8, 9, 11, 6
+    src = o.make_pool(L, H, D, nb_p, o.HND, seed=7)
+    dst = o.make_pool(L, H, D, nb_d, o.NHD, fill="canary")
+    ts, td = o.make_table(nb_p, n, 1), o.make_table(nb_d, n, 2)
+    o.handoff(src, ts, dst, td)
+    raw = o.make_pool(L, H, D, nb_d, o.NHD, fill="canary")
+    for r in range(2 * L):
+        cache = torch.from_numpy(raw.region_view(r).view(np.int16).reshape(nb_d, N, H, D))
+        cache.view(nb_d, -1)[torch.from_numpy(td.astype(np.int64))] = torch.from_numpy(
+            src.region_view(r).view(np.int16)[ts.astype(np.int64)].copy())
+        utils.kv_postprocess_layout_on_receive(cache, torch.from_numpy(td.astype(np.int64)))
+    assert np.array_equal(raw.buf, dst.buf)
