@@ -43,7 +43,7 @@ struct MemRecord {  // wire format of one exported device buffer
 struct PoolRecordHeader {  // wire format of an exported pool: header + regions x MemRecord
   uint32_t magic;
   uint32_t regions;
-  uint32_t block_tokens, heads, head_dim, elem_bytes, layout, tp_rank, tp_size, reserved;
+  uint32_t block_tokens, heads, head_dim, elem_bytes, layout, tp_rank, tp_size, head_stride;
   uint64_t num_blocks, block_stride;
 };
 
@@ -119,6 +119,7 @@ int64_t env_or(const char* name, int64_t dflt) {
 // ---- geometry ---------------------------------------------------------------------------------
 struct ChunkGeom {  // one side's chunk: H heads in `layout`, slice starts at head `off`, nb tokens per block
   uint32_t layout, heads, off, nb;
+  uint32_t hs = 0;  // HND only: bytes between consecutive heads of a chunk; 0 = nb * row (heads back to back)
 };
 
 struct Plan {
@@ -139,6 +140,11 @@ int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d,
   if (s.nb < N || d.nb < N || s.nb % N || d.nb % N) return KVX_EINVAL;
   const bool src_hnd = s.layout == KVX_LAYOUT_HND;
   const bool dst_hnd = d.layout == KVX_LAYOUT_HND;
+  // distance between heads of an HND chunk: nb rows when heads lie back to back, more in a cross-layer
+  // pool whose heads are the outermost dimension of a block ((nb, H, L, 2, N, D), [vllm] flash_attn.py:162-165)
+  const uint32_t shs = s.hs ? s.hs : s.nb * R, dhs = d.hs ? d.hs : d.nb * R;
+  if (src_hnd && (shs < s.nb * R || shs % 16u)) return KVX_EINVAL;
+  if (dst_hnd && (dhs < d.nb * R || dhs % 16u)) return KVX_EINVAL;
   const uint32_t major = src_hnd ? Hc : N;
   const uint32_t unit_bytes = src_hnd ? N * R : Hc * R;
   if (unit_bytes > cap) return KVX_EUNSUPPORTED;
@@ -155,15 +161,15 @@ int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d,
   p.s_sub_stride = src_hnd ? N * R : N * s.heads * R;
   p.d_sub_stride = dst_hnd ? N * R : N * d.heads * R;
   if (src_hnd) {
-    // image order (h, t); head h of the granule is N*R contiguous bytes, heads are s.nb*R apart
-    if (s.nb == N) { p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; }
-    else           { p.s_runs = g; p.s_run_bytes = N * R; p.s_stride = s.nb * R; }
-    p.s_slice_off = s.off * s.nb * R; p.s_piece_stride = g * s.nb * R;
+    // image order (h, t); head h of the granule is N*R contiguous bytes, heads are shs apart
+    if (shs == N * R) { p.s_runs = 1; p.s_run_bytes = p.piece_bytes; p.s_stride = 0; }
+    else              { p.s_runs = g; p.s_run_bytes = N * R; p.s_stride = shs; }
+    p.s_slice_off = s.off * shs; p.s_piece_stride = g * shs;
     if (dst_hnd) {
-      if (d.nb == N) { p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; }
-      else           { p.d_runs = g; p.d_run_bytes = N * R; p.d_n1 = 1; p.d_stride_a = d.nb * R; }
+      if (dhs == N * R) { p.d_runs = 1; p.d_run_bytes = p.piece_bytes; p.d_n1 = 1; p.d_stride_a = 0; }
+      else              { p.d_runs = g; p.d_run_bytes = N * R; p.d_n1 = 1; p.d_stride_a = dhs; }
       p.d_stride_b = 0;
-      p.d_slice_off = d.off * d.nb * R; p.d_piece_stride = g * d.nb * R;
+      p.d_slice_off = d.off * dhs; p.d_piece_stride = g * dhs;
     } else {
       // image order (h, t) → NHD row (t, off+h): run x = h*N + t
       p.d_runs = g * N; p.d_run_bytes = R; p.d_n1 = N; p.d_stride_a = R; p.d_stride_b = d.heads * R;
@@ -181,8 +187,8 @@ int32_t make_plan(uint32_t N, uint32_t R, uint32_t Hc, ChunkGeom s, ChunkGeom d,
       p.d_slice_off = d.off * R; p.d_piece_stride = g * d.heads * R;
     } else {
       // image order (t, h) → HND row (off+h, t): run x = t*Hc + h
-      p.d_runs = g * Hc; p.d_run_bytes = R; p.d_n1 = Hc; p.d_stride_a = R; p.d_stride_b = d.nb * R;
-      p.d_slice_off = d.off * d.nb * R; p.d_piece_stride = g * R;
+      p.d_runs = g * Hc; p.d_run_bytes = R; p.d_n1 = Hc; p.d_stride_a = R; p.d_stride_b = dhs;
+      p.d_slice_off = d.off * dhs; p.d_piece_stride = g * R;
     }
   }
   *out = p;
@@ -657,8 +663,8 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.n = n; ls.regions = s.regions;
   ls.N = std::min(s.block_tokens, d.block_tokens);  // granule = the smaller block
   ls.R = s.head_dim * s.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{s.layout, s.heads, so, s.block_tokens};
-  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
+  ls.sg = ChunkGeom{s.layout, s.heads, so, s.block_tokens, s.head_stride};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens, d.head_stride};
   ls.flag = flag;
   ls.flag_val = flag_val;
   ls.flag2 = flag2;
@@ -855,6 +861,11 @@ int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** ou
   if (chunk >= (1ull << 31)) return KVX_EUNSUPPORTED;
   const uint64_t stride = desc->block_stride ? desc->block_stride : chunk;
   if (stride < chunk || stride % 16 != 0) return KVX_EINVAL;
+  if (desc->head_stride != 0) {  // heads of a chunk spread apart (cross-layer HND pools)
+    if (desc->layout != KVX_LAYOUT_HND || desc->head_stride % 16 != 0 || desc->head_stride < row * desc->block_tokens ||
+        static_cast<uint64_t>(desc->head_stride) * desc->heads > stride)
+      return KVX_EINVAL;
+  }
   for (uint32_t r = 0; r < desc->regions; ++r) {
     if (!desc->base[r] || reinterpret_cast<uintptr_t>(desc->base[r]) % 16 != 0) return KVX_EINVAL;
   }
@@ -907,10 +918,13 @@ int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) {
   const kvx_pool_desc& d = pool->desc;
   h.magic = kPoolMagic; h.regions = d.regions; h.block_tokens = d.block_tokens; h.heads = d.heads;
   h.head_dim = d.head_dim; h.elem_bytes = d.elem_bytes; h.layout = d.layout; h.tp_rank = d.tp_rank;
-  h.tp_size = d.tp_size; h.num_blocks = d.num_blocks; h.block_stride = d.block_stride;
+  h.tp_size = d.tp_size; h.head_stride = d.head_stride; h.num_blocks = d.num_blocks; h.block_stride = d.block_stride;
   memcpy(buf, &h, sizeof(h));
   char* w = static_cast<char*>(buf) + sizeof(h);
-  const uint64_t span = (d.num_blocks - 1) * d.block_stride + pool->chunk_bytes;
+  const uint64_t row_bytes = static_cast<uint64_t>(d.head_dim) * d.elem_bytes;
+  const uint64_t chunk_extent = d.head_stride ? static_cast<uint64_t>(d.heads - 1) * d.head_stride + row_bytes * d.block_tokens
+                                              : pool->chunk_bytes;
+  const uint64_t span = (d.num_blocks - 1) * d.block_stride + chunk_extent;
   for (size_t r = 0; r < pool->base.size(); ++r) {
     MemRecord rec;
     int32_t rc = export_record(pool->ctx, pool->base[r], span, &rec);
@@ -944,7 +958,7 @@ int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** ou
   kvx_pool_desc d{};
   d.struct_size = sizeof(d); d.regions = h.regions; d.block_tokens = h.block_tokens; d.heads = h.heads;
   d.head_dim = h.head_dim; d.elem_bytes = h.elem_bytes; d.layout = h.layout; d.tp_rank = h.tp_rank;
-  d.tp_size = h.tp_size; d.num_blocks = h.num_blocks; d.block_stride = h.block_stride; d.base = bases.data();
+  d.tp_size = h.tp_size; d.head_stride = h.head_stride; d.num_blocks = h.num_blocks; d.block_stride = h.block_stride; d.base = bases.data();
   kvx_pool* pool = nullptr;
   rc = kvx_pool_register(ctx, &d, &pool);
   if (rc) {
@@ -1020,7 +1034,7 @@ int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, ui
   ls.dst = contiguous_side(staging, stage_chunk);
   ls.n = n; ls.regions = d.regions;
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
-  ls.sg = ChunkGeom{d.layout, d.heads, so, d.block_tokens};
+  ls.sg = ChunkGeom{d.layout, d.heads, so, d.block_tokens, d.head_stride};
   ls.dg = ChunkGeom{sl, hc, 0, d.block_tokens};
   return launch_xfer(ctx, ls, &src->base, nullptr, static_cast<cudaStream_t>(stream));
 }
@@ -1041,7 +1055,7 @@ int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, cons
   ls.n = n; ls.regions = d.regions;
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
   ls.sg = ChunkGeom{sl, hc, 0, d.block_tokens};
-  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens};
+  ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens, d.head_stride};
   return launch_xfer(ctx, ls, nullptr, &dst->base, static_cast<cudaStream_t>(stream));
 }
 
@@ -1273,6 +1287,9 @@ int32_t static_check_desc(const kvx_pool_desc* d, uint64_t* chunk, uint64_t* str
   if (*chunk >= (1ull << 31)) return KVX_EUNSUPPORTED;
   *stride = d->block_stride ? d->block_stride : *chunk;
   if (*stride < *chunk || *stride % 16 != 0) return KVX_EINVAL;
+  if (d->head_stride != 0 && (d->layout != KVX_LAYOUT_HND || d->head_stride % 16 != 0 || d->head_stride < row * d->block_tokens ||
+                              static_cast<uint64_t>(d->head_stride) * d->heads > *stride))
+    return KVX_EINVAL;
   for (uint32_t r = 0; r < d->regions; ++r)
     if (!d->base[r] || reinterpret_cast<uintptr_t>(d->base[r]) % 16 != 0) return KVX_EINVAL;
   return KVX_OK;
@@ -1322,8 +1339,8 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
 
   Plan pl{};
   rc = make_plan(src->block_tokens, src->head_dim * src->elem_bytes, hc,
-                 ChunkGeom{src->layout, src->heads, so, src->block_tokens},
-                 ChunkGeom{dst->layout, dst->heads, dof, dst->block_tokens}, kStaticStageBytes, &pl);
+                 ChunkGeom{src->layout, src->heads, so, src->block_tokens, src->head_stride},
+                 ChunkGeom{dst->layout, dst->heads, dof, dst->block_tokens, dst->head_stride}, kStaticStageBytes, &pl);
   if (rc) return rc;  // a head/token unit larger than one 16 KiB stage is not supported here
   const uint64_t total = static_cast<uint64_t>(n) * src->regions * pl.ppc;
   if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;

@@ -20,7 +20,7 @@ class PoolDesc(ctypes.Structure):
     _fields_ = [
         ("struct_size", c_u32), ("regions", c_u32), ("block_tokens", c_u32), ("heads", c_u32),
         ("head_dim", c_u32), ("elem_bytes", c_u32), ("layout", c_u32), ("tp_rank", c_u32),
-        ("tp_size", c_u32), ("reserved", c_u32), ("num_blocks", c_u64), ("block_stride", c_u64),
+        ("tp_size", c_u32), ("head_stride", c_u32), ("num_blocks", c_u64), ("block_stride", c_u64),
         ("base", P(c_vp)),
     ]
 

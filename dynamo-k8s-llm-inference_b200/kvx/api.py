@@ -164,10 +164,10 @@ class Context:
     # -- pools ----------------------------------------------------------------------------------
     def register_pool(self, bases: Sequence[int], *, num_blocks: int, heads: int, head_dim: int, layout: int,
                       block_tokens: int = 16, elem_bytes: int = 2, block_stride: int = 0, tp_rank: int = 0,
-                      tp_size: int = 1) -> Pool:
+                      tp_size: int = 1, head_stride: int = 0) -> Pool:
         arr = (c_vp * len(bases))(*[int(b) for b in bases])
         d = PoolDesc(ctypes.sizeof(PoolDesc), len(bases), block_tokens, heads, head_dim, elem_bytes, layout, tp_rank,
-                     tp_size, 0, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
+                     tp_size, head_stride, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
         h = c_vp()
         self._check(self.lib.kvx_pool_register(self.handle, ctypes.byref(d), ctypes.byref(h)), "kvx_pool_register")
         return Pool(self, h.value, regions=len(bases), block_tokens=block_tokens, heads=heads, head_dim=head_dim,
@@ -257,12 +257,12 @@ STATIC_MAX_REGIONS = 512
 
 
 def pool_desc(bases: Sequence[int], *, num_blocks: int, heads: int, head_dim: int, layout: int, block_tokens: int = 16,
-              elem_bytes: int = 2, block_stride: int = 0, tp_rank: int = 0, tp_size: int = 1):
+              elem_bytes: int = 2, block_stride: int = 0, tp_rank: int = 0, tp_size: int = 1, head_stride: int = 0):
     """A kvx_pool_desc for entry points that take descriptors rather than registered pools.  Returns
     (desc, keepalive): keep `keepalive` referenced for as long as `desc` is in use."""
     arr = (c_vp * len(bases))(*[int(b) for b in bases])
     d = PoolDesc(ctypes.sizeof(PoolDesc), len(bases), block_tokens, heads, head_dim, elem_bytes, layout, tp_rank,
-                 tp_size, 0, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
+                 tp_size, head_stride, num_blocks, block_stride, ctypes.cast(arr, ctypes.POINTER(c_vp)))
     return d, arr
 
 

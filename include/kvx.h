@@ -95,7 +95,11 @@ typedef struct kvx_pool_desc {
   uint32_t layout;       /* KVX_LAYOUT_NHD: [N][H][D]; KVX_LAYOUT_HND: [H][N][D] */
   uint32_t tp_rank;
   uint32_t tp_size;      /* sglang/disagg.yaml:41-42 (--tp)        */
-  uint32_t reserved;
+  uint32_t head_stride;  /* HND only: bytes between consecutive heads of one chunk; 0 = heads back to back
+                            (block_tokens * head_dim * elem_bytes).  Larger in cross-layer block pools
+                            whose heads are the outermost dimension of a block, (nb, H, L, 2, N, D)
+                            ([vllm] flash_attn.py:162-165): there head_stride = 2L * N * D * E, region
+                            (l, kv) starts (2l + kv) * N * D * E into the block, block_stride is the block */
   uint64_t num_blocks;
   uint64_t block_stride;
   void* const* base;     /* host array [regions] of device addresses */

@@ -587,3 +587,49 @@ def test_flag_wait_times_out_and_context_recovers(ctx):
     ctx.check()
     o.handoff(src, [2, 4], dst, [5, 1])
     assert np.array_equal(ddst.bytes(), dst.buf)
+
+
+def test_cross_layer_hnd_block_pools(cfg_ctx):
+    """vLLM's cross-layer pool in HND order is (num_blocks, H, L, 2, N, D) ([vllm] flash_attn.py:162-165): the
+    heads of one (layer, K|V) chunk lie 2L*N*D*E bytes apart.  kvx_pool_desc.head_stride describes it; checked
+    against numpy indexing of the engine's own 6-d array, both as source and (with a TP head slot) as destination."""
+    L, H, D, N, n, nb = 2, 4, 128, 16, 13, 22
+    E = 2
+    row, hs, blk = D * E, 2 * L * N * D * E, H * 2 * L * N * D * E
+    rng = np.random.Generator(np.random.PCG64(12))
+    a6 = rng.integers(0, 65536, size=(nb, H, L, 2, N, D), dtype=np.uint16)
+    t_src = torch.from_numpy(a6.view(np.int16)).cuda()
+    bases = [t_src.data_ptr() + (2 * l + kv) * N * row for l in range(L) for kv in range(2)]
+    src = cfg_ctx.register_pool(bases, num_blocks=nb, heads=H, head_dim=D, layout=kvx.HND, block_stride=blk, head_stride=hs)
+    dst = o.make_pool(L, H, D, nb + 2, o.NHD, fill="canary")
+    ddst = DevPool(cfg_ctx, dst)
+    ts, td = o.make_table(nb, n, 1), o.make_table(nb + 2, n, 2)
+    cfg_ctx.handoff_fused(src, dev_table(ts), ddst.kp, dev_table(td), n)
+    torch.cuda.synchronize()
+    got = ddst.bytes().view(np.uint16).reshape(2 * L, nb + 2, N, H, D)
+    for l in range(L):
+        for kv in range(2):
+            assert np.array_equal(got[2 * l + kv, td], a6[ts, :, l, kv].transpose(0, 2, 1, 3))
+    rest = np.ones(nb + 2, dtype=bool)
+    rest[td] = False
+    assert (got[:, rest] == o.CANARY16).all()
+    # destination side: two 2-head split HND sources into head slots 0 and 2 of a 4-head cross-layer HND pool
+    b6 = np.full((nb, H, L, 2, N, D), o.CANARY16, dtype=np.uint16)
+    t_dst = torch.from_numpy(b6.view(np.int16)).cuda()
+    dbases = [t_dst.data_ptr() + (2 * l + kv) * N * row for l in range(L) for kv in range(2)]
+    dpool = cfg_ctx.register_pool(dbases, num_blocks=nb, heads=H, head_dim=D, layout=kvx.HND, block_stride=blk, head_stride=hs)
+    want = b6.copy()
+    for s in range(2):
+        half = o.make_pool(L, 2, D, nb + 2, o.HND, seed=40 + s)
+        dhalf = DevPool(cfg_ctx, half)
+        cfg_ctx.handoff_fused(dhalf.kp, dev_table(td), dpool, dev_table(ts), n, kvx.Xform(0, 2 * s, 2, kvx.HND))
+        h5 = half.buf.view(np.uint16).reshape(2 * L, nb + 2, 2, N, D)
+        for l in range(L):
+            for kv in range(2):
+                want[ts, 2 * s:2 * s + 2, l, kv] = h5[2 * l + kv, td]
+    torch.cuda.synchronize()
+    assert np.array_equal(t_dst.cpu().numpy().view(np.uint16), want)
+    cfg_ctx.check()
+    src.release(); dpool.release()
+    with pytest.raises(kvx.KvxError):   # a head stride on an NHD pool makes no sense
+        cfg_ctx.register_pool(bases, num_blocks=nb, heads=H, head_dim=D, layout=kvx.NHD, block_stride=blk, head_stride=hs)
