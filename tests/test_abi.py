@@ -38,10 +38,12 @@ def test_version_and_strerror():
 
 
 def test_struct_sizes_match_header():
-    from kvx._lib import PoolDesc, XformC
+    from kvx._lib import BatchItem, PoolDesc, XformC
 
     assert ctypes.sizeof(PoolDesc) == 64
     assert ctypes.sizeof(XformC) == 16
+    assert ctypes.sizeof(BatchItem) == 48
+    assert PoolDesc.head_stride.offset == 36 and PoolDesc.num_blocks.offset == 40
 
 
 def test_no_cpu_fallback():
