@@ -99,6 +99,11 @@ int32_t cuda_fail(kvx_ctx* ctx, cudaError_t e, const char* what) {
     if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
   } while (0)
 
+// Nothing may leave the C ABI by exception: the containers used on the host side can throw bad_alloc.
+#define KVX_CATCH_ALL                               \
+  catch (const std::bad_alloc&) { return KVX_ENOMEM; } \
+  catch (...) { return KVX_EINVAL; }
+
 struct DeviceGuard {
   int prev = -1;
   bool ok = false;
@@ -706,7 +711,7 @@ const char* kvx_strerror(int32_t code) {
 
 const char* kvx_last_error(const kvx_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
 
-int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
+int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) try {
   if (!out) return KVX_EINVAL;
   *out = nullptr;
   int count = 0;
@@ -745,9 +750,9 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) {
   ctx->force_sys_fence = env_or("KVX_FORCE_SYS_FENCE", 0) != 0;
   *out = ctx;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_destroy(kvx_ctx* ctx) {
+int32_t kvx_ctx_destroy(kvx_ctx* ctx) try {
   if (!ctx) return KVX_EINVAL;
   {
     DeviceGuard guard(ctx->device);
@@ -763,9 +768,9 @@ int32_t kvx_ctx_destroy(kvx_ctx* ctx) {
   }
   delete ctx;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
+int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) try {
   if (!ctx || option < 0 || option >= KVX_OPT__COUNT) return KVX_EINVAL;
   switch (option) {
     case KVX_OPT_ENGINE: if (value < 0 || value > 2) return KVX_EINVAL; break;
@@ -783,27 +788,27 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) {
   }
   ctx->opt[option] = value;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_get_option(const kvx_ctx* ctx, int32_t option, int64_t* value) {
+int32_t kvx_ctx_get_option(const kvx_ctx* ctx, int32_t option, int64_t* value) try {
   if (!ctx || !value || option < 0 || option >= KVX_OPT__COUNT) return KVX_EINVAL;
   *value = ctx->opt[option];
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_launch_count(const kvx_ctx* ctx, uint64_t* count) {
+int32_t kvx_ctx_launch_count(const kvx_ctx* ctx, uint64_t* count) try {
   if (!ctx || !count) return KVX_EINVAL;
   *count = ctx->launches;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_sm_count(const kvx_ctx* ctx, int32_t* sms) {
+int32_t kvx_ctx_sm_count(const kvx_ctx* ctx, int32_t* sms) try {
   if (!ctx || !sms) return KVX_EINVAL;
   *sms = ctx->sms;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_mem_alloc(kvx_ctx* ctx, uint64_t bytes, void** out) {
+int32_t kvx_mem_alloc(kvx_ctx* ctx, uint64_t bytes, void** out) try {
   if (!ctx || !out || bytes == 0) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   cudaError_t e = cudaMalloc(out, bytes);
@@ -813,16 +818,16 @@ int32_t kvx_mem_alloc(kvx_ctx* ctx, uint64_t bytes, void** out) {
   }
   if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaMalloc");
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_mem_free(kvx_ctx* ctx, void* ptr) {
+int32_t kvx_mem_free(kvx_ctx* ctx, void* ptr) try {
   if (!ctx) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   KVX_CUDA(ctx, cudaFree(ptr));
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_mem_export(kvx_ctx* ctx, const void* ptr, uint64_t bytes, void* buf, size_t* len) {
+int32_t kvx_mem_export(kvx_ctx* ctx, const void* ptr, uint64_t bytes, void* buf, size_t* len) try {
   if (!ctx || !ptr || !len) return KVX_EINVAL;
   if (!buf || *len < sizeof(MemRecord)) {
     *len = sizeof(MemRecord);
@@ -834,21 +839,21 @@ int32_t kvx_mem_export(kvx_ctx* ctx, const void* ptr, uint64_t bytes, void* buf,
   memcpy(buf, &rec, sizeof(rec));
   *len = sizeof(rec);
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_mem_import(kvx_ctx* ctx, const void* buf, size_t len, void** out) {
+int32_t kvx_mem_import(kvx_ctx* ctx, const void* buf, size_t len, void** out) try {
   if (!ctx || !buf || !out || len < sizeof(MemRecord)) return KVX_EINVAL;
   MemRecord rec;
   memcpy(&rec, buf, sizeof(rec));
   return import_record(ctx, &rec, out);
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_mem_unmap(kvx_ctx* ctx, void* imported) {
+int32_t kvx_mem_unmap(kvx_ctx* ctx, void* imported) try {
   if (!ctx || !imported) return KVX_EINVAL;
   return unmap_ptr(ctx, imported);
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** out) {
+int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** out) try {
   if (!ctx || !desc || !out || !desc->base) return KVX_EINVAL;
   if (desc->struct_size != sizeof(kvx_pool_desc)) return KVX_EINVAL;
   if (desc->regions == 0 || desc->block_tokens == 0 || desc->heads == 0 || desc->head_dim == 0 ||
@@ -889,9 +894,9 @@ int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** ou
   }
   *out = pool;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_pool_release(kvx_pool* pool) {
+int32_t kvx_pool_release(kvx_pool* pool) try {
   if (!pool) return KVX_EINVAL;
   DeviceGuard guard(pool->ctx->device);
   for (void* p : pool->imported_ptrs) unmap_ptr(pool->ctx, p);
@@ -899,15 +904,15 @@ int32_t kvx_pool_release(kvx_pool* pool) {
   (void)cudaGetLastError();
   delete pool;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes) {
+int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes) try {
   if (!pool || !bytes) return KVX_EINVAL;
   *bytes = pool->chunk_bytes;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) {
+int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) try {
   if (!pool || !len) return KVX_EINVAL;
   const size_t need = sizeof(PoolRecordHeader) + pool->base.size() * sizeof(MemRecord);
   if (!buf || *len < need) {
@@ -933,9 +938,9 @@ int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) {
   }
   *len = need;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out) {
+int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out) try {
   if (!ctx || !buf || !out || len < sizeof(PoolRecordHeader)) return KVX_EINVAL;
   PoolRecordHeader h;
   memcpy(&h, buf, sizeof(h));
@@ -968,23 +973,23 @@ int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** ou
   pool->imported_ptrs = bases;
   *out = pool;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_flags(kvx_ctx* ctx, uint64_t** flags, uint32_t* count) {
+int32_t kvx_ctx_flags(kvx_ctx* ctx, uint64_t** flags, uint32_t* count) try {
   if (!ctx || !flags || !count) return KVX_EINVAL;
   *flags = ctx->d_flags;
   *count = kNumFlags;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_flag_reset(kvx_ctx* ctx, uint64_t* flag, uint64_t value, void* stream) {
+int32_t kvx_flag_reset(kvx_ctx* ctx, uint64_t* flag, uint64_t value, void* stream) try {
   if (!ctx || !flag) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   KVX_CUDA(ctx, cudaMemcpyAsync(flag, &value, sizeof(value), cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_flag_wait(kvx_ctx* ctx, const uint64_t* flag, uint64_t value, uint32_t timeout_ms, void* stream) {
+int32_t kvx_flag_wait(kvx_ctx* ctx, const uint64_t* flag, uint64_t value, uint32_t timeout_ms, void* stream) try {
   if (!ctx || !flag) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   const unsigned long long ns = static_cast<unsigned long long>(timeout_ms ? timeout_ms : 1000u) * 1000000ull;
@@ -993,18 +998,18 @@ int32_t kvx_flag_wait(kvx_ctx* ctx, const uint64_t* flag, uint64_t value, uint32
   KVX_CUDA(ctx, cudaGetLastError());
   ctx->launches++;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_flag_poll(kvx_ctx* ctx, const uint64_t* flag, uint64_t value) {
+int32_t kvx_flag_poll(kvx_ctx* ctx, const uint64_t* flag, uint64_t value) try {
   if (!ctx || !flag) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   uint64_t cur = 0;
   KVX_CUDA(ctx, cudaMemcpyAsync(&cur, flag, sizeof(cur), cudaMemcpyDeviceToHost, ctx->aux));
   KVX_CUDA(ctx, cudaStreamSynchronize(ctx->aux));
   return cur >= value ? KVX_OK : KVX_ENOTREADY;
-}
+} KVX_CATCH_ALL
 
-int32_t kvx_ctx_check(kvx_ctx* ctx) {
+int32_t kvx_ctx_check(kvx_ctx* ctx) try {
   if (!ctx) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
   unsigned st = 0;
@@ -1017,10 +1022,10 @@ int32_t kvx_ctx_check(kvx_ctx* ctx) {
   if (st & kvx::kStatusWaitTimeout) return KVX_ETIMEOUT;
   if (st & kvx::kStatusBadBlockId) return KVX_ERANGE;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, uint32_t n, void* staging,
-                   const kvx_xform* xf, void* stream) {
+                   const kvx_xform* xf, void* stream) try {
   if (!ctx || !src) return KVX_EINVAL;
   if (n == 0) return KVX_OK;
   if (!d_table || !staging || reinterpret_cast<uintptr_t>(staging) % 16 != 0) return KVX_EINVAL;
@@ -1037,10 +1042,10 @@ int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, ui
   ls.sg = ChunkGeom{d.layout, d.heads, so, d.block_tokens, d.head_stride};
   ls.dg = ChunkGeom{sl, hc, 0, d.block_tokens};
   return launch_xfer(ctx, ls, &src->base, nullptr, static_cast<cudaStream_t>(stream));
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, const int32_t* d_table, uint32_t n,
-                    const kvx_xform* xf, void* stream) {
+                    const kvx_xform* xf, void* stream) try {
   if (!ctx || !dst) return KVX_EINVAL;
   if (n == 0) return KVX_OK;
   if (!d_table || !staging || reinterpret_cast<uintptr_t>(staging) % 16 != 0) return KVX_EINVAL;
@@ -1057,10 +1062,10 @@ int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, cons
   ls.sg = ChunkGeom{sl, hc, 0, d.block_tokens};
   ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens, d.head_stride};
   return launch_xfer(ctx, ls, nullptr, &dst->base, static_cast<cudaStream_t>(stream));
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint64_t* flag, uint64_t flag_val,
-                 void* stream) {
+                 void* stream) try {
   if (!ctx) return KVX_EINVAL;
   if (bytes != 0 && (!src || !dst)) return KVX_EINVAL;
   if (bytes % 16 != 0 || reinterpret_cast<uintptr_t>(src) % 16 != 0 || reinterpret_cast<uintptr_t>(dst) % 16 != 0)
@@ -1086,19 +1091,19 @@ int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint6
     return KVX_OK;
   }
   return launch_xfer(ctx, ls, nullptr, nullptr, static_cast<cudaStream_t>(stream));
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_table, const kvx_pool* dst,
                           const int32_t* d_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag,
-                          uint64_t flag_val, void* stream) {
+                          uint64_t flag_val, void* stream) try {
   if (!ctx || !src || !dst) return KVX_EINVAL;
   if (n != 0 && (!d_src_table || !d_dst_table)) return KVX_EINVAL;
   return handoff_impl(ctx, src, d_src_table, dst, d_dst_table, n, xf, flag, flag_val, stream, nullptr, nullptr, nullptr);
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table, const kvx_pool* dst,
                          const int32_t* h_dst_table, uint32_t n, const kvx_xform* xf, uint64_t* flag,
-                         uint64_t flag_val, uint64_t* h_done, void* stream) {
+                         uint64_t flag_val, uint64_t* h_done, void* stream) try {
   if (!ctx || !src || !dst) return KVX_EINVAL;
   if (n > KVX_MAX_HOST_TABLE) return KVX_ERANGE;
   if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
@@ -1150,10 +1155,10 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
     KVX_CUDA(ctx, cudaMemcpyAsync(h_done, f, sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
   }
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
 int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, const kvx_batch_item* items,
-                          uint32_t count, const kvx_xform* xf, void* stream) {
+                          uint32_t count, const kvx_xform* xf, void* stream) try {
   if (!ctx || !src || !dst || (count != 0 && !items)) return KVX_EINVAL;
   if (!same_shape(src->desc, dst->desc)) return KVX_EINVAL;
   if (count == 0) return KVX_OK;
@@ -1210,7 +1215,7 @@ int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst
     if (rc) return rc;
   }
   return KVX_OK;
-}
+} KVX_CATCH_ALL
 
 }  // extern "C"
 
@@ -1299,7 +1304,7 @@ int32_t static_check_desc(const kvx_pool_desc* d, uint64_t* chunk, uint64_t* str
 
 extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, const int32_t* h_src_table,
                                       const kvx_pool_desc* dst, const int32_t* h_dst_table, uint32_t n,
-                                      const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream) {
+                                      const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream) try {
   if (device < 0 || device >= kStaticMaxDevices) return KVX_EINVAL;
   if (n > KVX_STATIC_MAX_BLOCKS) return KVX_ERANGE;  // beyond the fixed table capacity
   uint64_t s_chunk = 0, s_stride = 0, d_chunk = 0, d_stride = 0;
@@ -1385,4 +1390,4 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   kvx::kvx_xfer_tma_kernel<16, 8><<<grid, 32u * (1u + kStaticConsumerWarps), kStaticStages * kStaticStageBytes, st>>>(p);
   if (bad(cudaGetLastError())) return KVX_ECUDA;
   return KVX_OK;
-}
+} KVX_CATCH_ALL
