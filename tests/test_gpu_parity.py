@@ -633,3 +633,39 @@ def test_cross_layer_hnd_block_pools(cfg_ctx):
     src.release(); dpool.release()
     with pytest.raises(kvx.KvxError):   # a head stride on an NHD pool makes no sense
         cfg_ctx.register_pool(bases, num_blocks=nb, heads=H, head_dim=D, layout=kvx.NHD, block_stride=blk, head_stride=hs)
+
+
+def test_many_streams_many_flags(ctx):
+    """160 handoffs from 8 streams into disjoint blocks of one pool, each with its own completion flag:
+    the per-launch counter ring, dependent launches and flags must not interfere across streams."""
+    L, H, D = 1, 8, 64
+    S, PER, nmax = 8, 20, 6
+    nb = S * PER * nmax + 1
+    src = o.make_pool(L, H, D, nb, o.HND, seed=8)
+    dst = o.make_pool(L, H, D, nb, o.NHD, fill="canary")
+    dsrc, ddst = DevPool(ctx, src), DevPool(ctx, dst)
+    rng = np.random.Generator(np.random.PCG64(4))
+    ids_s = 1 + rng.permutation(nb - 1)
+    ids_d = 1 + rng.permutation(nb - 1)
+    flags, nflags = ctx.flags()
+    streams = [torch.cuda.Stream() for _ in range(S)]
+    jobs, at = [], 0
+    for k in range(S * PER):
+        n = int(rng.integers(1, nmax + 1))
+        jobs.append((ids_s[at:at + n].astype(np.int32), ids_d[at:at + n].astype(np.int32)))
+        ctx.flag_reset(flags + 8 * (100 + k), 0)
+        at += n
+    tabs = [(dev_table(a), dev_table(b)) for a, b in jobs]
+    torch.cuda.synchronize()
+    for k, (a, b) in enumerate(jobs):
+        st = streams[k % S]
+        if k % 3 == 0:   # a third through the host-table entry
+            ctx.handoff_host(dsrc.kp, a, ddst.kp, b, len(a), None, flags + 8 * (100 + k), k + 1, None, st)
+        else:
+            ctx.handoff_fused(dsrc.kp, tabs[k][0], ddst.kp, tabs[k][1], len(a), None, flags + 8 * (100 + k), k + 1, st)
+    torch.cuda.synchronize()
+    ctx.check()
+    for k, (a, b) in enumerate(jobs):
+        assert ctx.flag_poll(flags + 8 * (100 + k), k + 1), k
+        o.handoff(src, a, dst, b)
+    assert np.array_equal(ddst.bytes(), dst.buf)
