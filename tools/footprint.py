@@ -26,8 +26,9 @@ D = synth.alloc_pool(dctx, shape, nb, kvx.NHD)
 synth.fill_random(P, 3)
 torch.cuda.set_device(dev)
 src = dctx.import_pool(P.pool.export()) if two else P.pool
-ts = [torch.from_numpy(synth.make_table(nb, n, 1 + k)).cuda(dev) for k in range(2)]
-td = [torch.from_numpy(synth.make_table(nb, n, 5 + k)).cuda(dev) for k in range(2)]
+contig = os.environ.get("TABLES", "random") == "contig"   # best-case control: ascending block ids on both sides
+ts = [torch.from_numpy(np.arange(1 + k * n, 1 + (k + 1) * n, dtype=np.int32) if contig else synth.make_table(nb, n, 1 + k)).cuda(dev) for k in range(2)]
+td = [torch.from_numpy(np.arange(1 + k * n, 1 + (k + 1) * n, dtype=np.int32) if contig else synth.make_table(nb, n, 5 + k)).cuda(dev) for k in range(2)]
 stream = torch.cuda.current_stream(dev)
 payload = n * shape.regions * shape.chunk_bytes()
 
@@ -48,6 +49,8 @@ def timed(reps=6):
 dctx.set_option("max_ctas", 0)
 t = timed()
 print(json.dumps({"path": "nvlink_pull" if two else "intra_device", "defaults": True, "ms": round(t, 4), "payload_GBps": round(payload / t / 1e6, 1)}), flush=True)
+if os.environ.get("DEFAULTS_ONLY"):
+    sys.exit(0)
 for stages, sb in ((4, 16384), (6, 32768)):
     dctx.set_option("stages", stages)
     dctx.set_option("stage_bytes", sb)
