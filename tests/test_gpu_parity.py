@@ -669,3 +669,29 @@ def test_many_streams_many_flags(ctx):
         assert ctx.flag_poll(flags + 8 * (100 + k), k + 1), k
         o.handoff(src, a, dst, b)
     assert np.array_equal(ddst.bytes(), dst.buf)
+
+
+@pytest.mark.parametrize("dst_layout", [o.NHD, o.HND], ids=["to_nhd", "identity"])
+def test_baseline_config1_exact_size(ctx, dst_layout):
+    """BASELINE.json configs[0] at its exact size (Llama-3.2-1B KV shape, one 2k-token prompt, 64 MiB): the
+    kernel against the oracle, fused and gather -> copy -> scatter."""
+    L, H, D, n = 16, 8, 64, 128
+    nb = 4 * n + 1
+    src = o.make_pool(L, H, D, nb, o.HND, seed=0xD15A66 + 1000)
+    want = o.make_pool(L, H, D, nb, dst_layout, fill="canary")
+    ts, td = o.make_table(nb, n, 0xD15A66 + 1007), o.make_table(nb, n, 0xD15A66 + 1013)
+    o.handoff(src, ts, want, td)
+    dsrc = DevPool(ctx, src)
+    d1 = DevPool(ctx, o.make_pool(L, H, D, nb, dst_layout, fill="canary"))
+    d2 = DevPool(ctx, o.make_pool(L, H, D, nb, dst_layout, fill="canary"))
+    ctx.handoff_host(dsrc.kp, ts, d1.kp, td, n)
+    img = torch.empty(n * src.regions * src.chunk_bytes, dtype=torch.uint8, device="cuda")
+    img2 = torch.empty_like(img)
+    xf = kvx.Xform(0, 0, 0, dst_layout)
+    ctx.gather(dsrc.kp, dev_table(ts), n, img, xf)
+    ctx.copy(img, img2, img.numel())
+    ctx.scatter(img2, d2.kp, dev_table(td), n, xf)
+    torch.cuda.synchronize()
+    ctx.check()
+    assert np.array_equal(d1.bytes(), want.buf)
+    assert np.array_equal(d2.bytes(), want.buf)

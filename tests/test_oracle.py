@@ -274,3 +274,24 @@ def test_live_vllm_helper_agrees_with_oracle():
             src.region_view(r).view(np.int16)[ts.astype(np.int64)].copy())
         utils.kv_postprocess_layout_on_receive(cache, torch.from_numpy(td.astype(np.int64)))
     assert np.array_equal(raw.buf, dst.buf)
+
+
+def test_baseline_config1_exact_size_numpy_vs_c():
+    """BASELINE.json configs[0]: Llama-3.2-1B KV shape (16 layers, 8 KV heads, d=64, bf16, 16-token blocks), one
+    2k-token prompt = 128 blocks x 32 regions x 16 KiB = 64 MiB, prefill HND -> decode NHD and identity; the two
+    CPU restatements (NumPy, C with 1 and 4 threads) agree on every byte of the decode pool."""
+    L, H, D, n = 16, 8, 64, 128
+    nb = 4 * n + 1
+    src = o.make_pool(L, H, D, nb, o.HND, seed=0xD15A66 + 1000)
+    ts, td = o.make_table(nb, n, 0xD15A66 + 1007), o.make_table(nb, n, 0xD15A66 + 1013)
+    assert n * src.regions * src.chunk_bytes == 64 << 20
+    for layout in (o.NHD, o.HND):
+        want = o.make_pool(L, H, D, nb, layout, fill="canary")
+        o.handoff(src, ts, want, td)
+        for threads in (1, 4):
+            got = o.make_pool(L, H, D, nb, layout, fill="canary")
+            assert oc.handoff(src, ts, got, td, threads=threads) == 0
+            assert np.array_equal(got.buf, want.buf)
+        untouched = np.ones(nb, dtype=bool)
+        untouched[td] = False
+        assert (want.region_view(0)[untouched].view(np.uint16) == o.CANARY16).all()
