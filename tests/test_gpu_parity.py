@@ -695,3 +695,46 @@ def test_baseline_config1_exact_size(ctx, dst_layout):
     ctx.check()
     assert np.array_equal(d1.bytes(), want.buf)
     assert np.array_equal(d2.bytes(), want.buf)
+
+
+def test_full_size_properties_tp4_to_tp2_llama70b():
+    """BASELINE config #4 at full size on one GPU (Llama-3.1-70B KV shape, ISL 8192: two prefill TP4 shards of
+    2 heads -> one decode TP2 shard of 4 heads, 640 MiB per edge), checked by size-independent properties:
+    every head slot of the decode chunk equals its source shard's chunk (HND -> NHD), and sending the slots back
+    (TP2 -> TP4 direction, head slice on the source side) restores both shards bit for bit."""
+    from kvx import synth
+
+    c = kvx.Context(0)
+    shape = kvx.KV_SHAPES["meta-llama/Llama-3.1-70B"]
+    n = shape.blocks_for(8192)
+    nb = n + 77
+    P = [synth.alloc_pool(c, shape, nb, kvx.HND, heads=2, tp_rank=r, tp_size=4) for r in range(2)]
+    Dp = synth.alloc_pool(c, shape, nb, kvx.NHD, heads=4, tp_rank=0, tp_size=2)
+    back = [synth.alloc_pool(c, shape, nb, kvx.HND, heads=2, tp_rank=r, tp_size=4) for r in range(2)]
+    for r in range(2):
+        synth.fill_random(P[r], 700 + r)
+        synth.fill_canary(back[r])
+    synth.fill_canary(Dp)
+    tp, td, tb = (synth.make_table(nb, n, s) for s in (1, 2, 3))
+    dtp, dtd, dtb = dev_table(tp), dev_table(td), dev_table(tb)
+    for r in range(2):
+        c.handoff_fused(P[r].pool, dtp, Dp.pool, dtd, n, kvx.Xform(0, 2 * r, 2, kvx.NHD))      # slot r of the decode chunk
+    for r in range(2):
+        c.handoff_fused(Dp.pool, dtd, back[r].pool, dtb, n, kvx.Xform(2 * r, 0, 2, kvx.HND))   # head slice back out
+    torch.cuda.synchronize()
+    c.check()
+    N, Dh, R = shape.block_tokens, shape.head_dim, shape.regions
+    ip, idd, ib = (torch.from_numpy(t.astype(np.int64)).cuda() for t in (tp, td, tb))
+    dview = Dp.tensor().view(torch.int16).view(R, nb, N, 4, Dh)[:, idd]
+    for r in range(2):
+        a = P[r].tensor().view(torch.int16).view(R, nb, 2, N, Dh)[:, ip]
+        b = back[r].tensor().view(torch.int16).view(R, nb, 2, N, Dh)[:, ib]
+        assert torch.equal(a, b)
+        assert torch.equal(a.transpose(2, 3), dview[:, :, :, 2 * r:2 * r + 2])
+    canary = np.array(synth.CANARY16, dtype=np.uint16).view(np.int16).item()
+    mask = torch.ones(nb, dtype=torch.bool, device="cuda")
+    mask[idd] = False
+    assert (Dp.tensor().view(torch.int16).view(R, nb, -1)[:, mask] == canary).all()
+    for p in P + back + [Dp]:
+        p.free()
+    c.close()
