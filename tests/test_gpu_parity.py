@@ -294,11 +294,21 @@ def test_full_size_properties_qwen3_32k(cfg):
     """BASELINE config #2 at its largest size (Qwen3-0.6B KV shape, ISL 32k, 3.5 GiB payload), checked
     by size-independent properties on the device: HND→NHD→HND round trip restores the request's
     blocks bit for bit, a word checksum is preserved by each hop, untouched blocks keep the canary."""
+    _round_trip_properties(cfg, "Qwen/Qwen3-0.6B", 32768)
+
+
+def test_full_size_properties_llama8b_32k():
+    """BASELINE configs #3 / #5 at their largest request (Llama-3.1-8B KV shape, ISL 32k, 4 GiB payload), the
+    same properties on one GPU (the multi-GPU runs verify the NVLink path bit for bit through the harness)."""
+    _round_trip_properties({}, "meta-llama/Llama-3.1-8B", 32768)
+
+
+def _round_trip_properties(cfg, model, isl):
     from kvx import synth
 
     c = kvx.Context(0, **cfg)
-    shape = kvx.KV_SHAPES["Qwen/Qwen3-0.6B"]
-    n = shape.blocks_for(32768)
+    shape = kvx.KV_SHAPES[model]
+    n = shape.blocks_for(isl)
     nb = n + 129
     P = synth.alloc_pool(c, shape, nb, kvx.HND)
     Dp = synth.alloc_pool(c, shape, nb, kvx.NHD)
