@@ -5,7 +5,7 @@
 Same required flags, same messages, same exit codes.  `-u` is either an OpenAI-compatible HTTP endpoint, as
 in the reference (driven by kvx/httpload.py with the shape of the reference's multi_convos_parallel.sh), or a
 transport URL:  kvx://local?manifest=<DynamoGraphDeployment yaml>[&isl=8192][&requests=64][&concurrency=1]
-           kvx://local?prefill=4&decode=4[&ptp=4&dtp=2][&isl=1024,2048,...][&layout=nhd][&route=spread]
+           kvx://local?prefill=4&decode=4[&ptp=4&dtp=2][&isl=1024,2048,...][&layout=nhd][&route=spread][&batch=8]
 Results land under <output-dir>/<benchmark-name>/results.json; -p adds SVG plots from that tree.
 """
 from __future__ import annotations
@@ -94,7 +94,7 @@ def build_job(url: str, model: str):
     isl = [isls[0]] * requests if len(isls) == 1 else draw_isls(requests, isls, int(q.get("seed", 5)))
     opts = {k: int(q[k]) for k in ("engine", "stages", "stage_bytes", "ctas_per_sm", "store_mode", "vec_bytes", "consumer_warps") if k in q}
     cfg = StreamConfig(model=model, isl=isl, concurrency=int(q.get("concurrency", 1)), verify=q.get("verify", "1") != "0",
-                       decode_layout=layout, options=opts, route=q.get("route", "pair"))
+                       decode_layout=layout, options=opts, route=q.get("route", "pair"), batch=int(q.get("batch", 1)))
     return topo, cfg
 
 

@@ -36,6 +36,8 @@ class StreamConfig:
     concurrency: int = 1
     verify: bool = True
     decode_layout: Optional[int] = None  # None = manifest's
+    batch: int = 1  # > 1: the decode worker pulls this many queued requests per scheduler step in ONE launch
+    #                  (kvx_handoff_batch; same-size TP only, route "pair")
     route: str = "pair"  # "pair": decode replica i reads prefill replica i % nP; "spread": request q of decode
     #                       replica i reads prefill replica (i + q) % nP (with concurrency >= nP this is an incast)
     options: Dict[str, int] = field(default_factory=dict)  # kvx context options
@@ -163,7 +165,26 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
         dist.barrier()
         torch.cuda.synchronize()
         t_begin = time.perf_counter()
+        batch = cfg.batch if (cfg.batch > 1 and len(srcs) == 1 and p_tp == d_tp and cfg.route == "pair") else 1
+        group_of = {}
+        if batch > 1:
+            # one scheduler step = up to `batch` queued requests, received in one launch; closed loop over steps
+            lane0 = streams[0][0]
+            key = src_replica(me.replica, 0) * 1000 + srcs[0].p_rank
+            for g0 in range(0, len(counts), batch):
+                qs = list(range(g0, min(len(counts), g0 + batch)))
+                t0 = time.perf_counter()
+                ev[g0][0].record(lane0)
+                w.pull_many(key, [(remote_ids[q], local_ids[q], (q * d_tp + me.tp_rank) % w.num_flags, q + 1, None) for q in qs],
+                            stream=lane0)
+                ev[g0][1].record(lane0)
+                ev[g0][1].synchronize()
+                t1 = time.perf_counter()
+                for q in qs:
+                    t_sub[q], t_done[q], group_of[q] = t0, t1, (g0, qs)
         for q, n in enumerate(counts):
+            if batch > 1:
+                break
             if q >= c:  # closed loop: at most c requests in flight
                 ev[q - c][1].synchronize()
                 t_done[q - c] = time.perf_counter()
@@ -182,6 +203,8 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
                 lane[0].wait_event(done_j)
             ev[q][1].record(lane[0])
         for q in range(max(0, len(counts) - c), len(counts)):
+            if batch > 1:
+                break
             ev[q][1].synchronize()
             t_done[q] = time.perf_counter()
         torch.cuda.synchronize()
@@ -189,10 +212,16 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
         w.ctx.check()
         for q, n in enumerate(counts):
             b = n * shape.regions * chunk_local
-            xfer = ev[q][0].elapsed_time(ev[q][1]) / 1e3
+            if q in group_of:  # batched: the step's requests complete together; rate = the step's bytes over its time
+                g0, qs = group_of[q]
+                xfer = ev[g0][0].elapsed_time(ev[g0][1]) / 1e3
+                rate = sum(counts[x] for x in qs) * shape.regions * chunk_local / xfer / 1e9
+            else:
+                xfer = ev[q][0].elapsed_time(ev[q][1]) / 1e3
+                rate = b / xfer / 1e9
             per_req.append({"request": q, "isl": cfg.isl[q], "num_blocks": n, "bytes_transferred": b,
                             "num_descriptors": n * shape.regions * len(srcs), "xfer_time_seconds": xfer,
-                            "throughput_GBps": b / xfer / 1e9,
+                            "throughput_GBps": rate, "batched_with": len(group_of[q][1]) if q in group_of else 1,
                             "time_to_first_token_added_ms": 1e3 * (t_done[q] - t_sub[q])})
         ok = True
         if cfg.verify:
