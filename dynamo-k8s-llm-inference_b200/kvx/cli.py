@@ -92,7 +92,8 @@ def build_job(url: str, model: str):
     requests = int(q.get("requests", 16))
     isls = [int(x) for x in q.get("isl", "8192").split(",")]
     isl = [isls[0]] * requests if len(isls) == 1 else draw_isls(requests, isls, int(q.get("seed", 5)))
-    opts = {k: int(q[k]) for k in ("engine", "stages", "stage_bytes", "ctas_per_sm", "store_mode", "vec_bytes", "consumer_warps") if k in q}
+    opts = {k: int(q[k]) for k in ("engine", "stages", "stage_bytes", "ctas_per_sm", "store_mode", "vec_bytes", "consumer_warps", "l2_hint", "pdl",
+                                   "param_tables", "max_ctas") if k in q}
     cfg = StreamConfig(model=model, isl=isl, concurrency=int(q.get("concurrency", 1)), verify=q.get("verify", "1") != "0",
                        decode_layout=layout, options=opts, route=q.get("route", "pair"), batch=int(q.get("batch", 1)))
     return topo, cfg

@@ -120,7 +120,9 @@ def test_build_job_from_url(tmp_path):
     assert topo.name == "t-disagg" and len(cfg.isl) == 9 and set(cfg.isl) <= {1024, 4096} and cfg.concurrency == 2
     assert cfg.options == {"stages": 3}
     topo, cfg = build_job("kvx://local?prefill=4&decode=4&isl=8192&requests=3", "meta-llama/Llama-3.1-8B")
-    assert [w.replicas for w in topo.workers] == [4, 4] and cfg.isl == [8192] * 3
+    assert [w.replicas for w in topo.workers] == [4, 4] and cfg.isl == [8192] * 3 and cfg.batch == 1
+    _, cfg = build_job("kvx://local?prefill=1&decode=1&isl=128&requests=16&batch=8&max_ctas=32", "meta-llama/Llama-3.1-8B")
+    assert cfg.batch == 8 and cfg.options == {"max_ctas": 32}
 
 
 def test_plots_from_results(tmp_path):
