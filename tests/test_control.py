@@ -75,3 +75,46 @@ def test_guarded_pull_reports_invalid_blocks():
     assert not out.ok and out.invalid_block_ids.tolist() == [7, 8, 9, 10] and "longer" in out.detail
     out = c.guarded_pull(Fine(), 0, params, [7, 8, 9])
     assert out.ok and out.invalid_block_ids.size == 0
+
+
+def test_bootstrap_handshake_over_tcp():
+    """Two workers shake hands over the bootstrap port (the manifests' --disaggregation-bootstrap-port role):
+    records cross intact, a per-request record follows on the same connection, an incompatible peer is refused."""
+    from kvx import bootstrap as b
+
+    kw = dict(regions=64, head_dim=128, elem_bytes=2, total_kv_heads=8)
+    good = c.compat_hash(abi=0x00010000, **kw)
+    p_meta = WorkerMetadata("prefill", 0, 1, 1, 4097, 16, 8, b"P" * 5000, b"pf" * 40, 4096)
+    seen, requests = [], []
+
+    def on_peer(rec, addr):
+        seen.append(c.decode_metadata(rec, expect_compat=good))   # raises WireError for a stranger
+
+    def on_frame(frame, addr):
+        requests.append(c.decode_params(frame))
+        return c.encode_heartbeat([requests[-1].request_id])
+
+    srv = b.BootstrapServer(c.encode_metadata(p_meta, **kw), on_peer, on_frame=on_frame)
+    try:
+        host, port = srv.address
+        cli = b.BootstrapClient(host, port, c.encode_metadata(_meta(), **kw))
+        assert c.decode_metadata(cli.peer_record, expect_compat=good) == p_meta
+        assert seen == [_meta()]
+        reply = cli.send(c.encode_params(TransferParams("req-7", np.array([3, 1, 4, 1, 5], np.int32), 0, 1)), expect_reply=True)
+        assert c.decode_heartbeat(reply) == ["req-7"]
+        assert requests[0].remote_block_ids.tolist() == [3, 1, 4, 1, 5]
+        cli.close()
+        # a peer built for another head_dim: the server refuses it and sends nothing back
+        with pytest.raises(c.WireError, match="handshake"):
+            b.BootstrapClient(host, port, c.encode_metadata(_meta(), **{**kw, "head_dim": 64}), timeout=3.0)
+        assert len(seen) == 1 and any("incompatible" in e for e in srv.errors)
+        # garbage on the port is an error, not a crash
+        import socket
+
+        with socket.create_connection((host, port), timeout=3) as s:
+            s.sendall(b"GET / HTTP/1.1\r\n\r\n")
+        cli2 = b.BootstrapClient(host, port, c.encode_metadata(_meta(), **kw))
+        assert len(seen) == 2
+        cli2.close()
+    finally:
+        srv.close()

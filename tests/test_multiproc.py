@@ -111,3 +111,22 @@ def test_in_process_peer_handoff():
     torch.cuda.synchronize(0); torch.cuda.synchronize(1)
     assert np.array_equal(d.kv.to_numpy(), want.buf)
     p.close(); d.close()
+
+
+@pytest.mark.gpu
+def test_bootstrap_port_pair(tmp_path):
+    """Two independent processes (no torchrun): handshake over the bootstrap port, pull over CUDA IPC, release,
+    lease bookkeeping on the prefill side — the whole control + data path of one request."""
+    script = os.path.join(ROOT, "tests", "bootstrap_pair.py")
+    portfile = str(tmp_path / "port")
+    p = subprocess.Popen([sys.executable, script, "prefill", portfile], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    d = subprocess.Popen([sys.executable, script, "decode", portfile], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        d_out, _ = d.communicate(timeout=240)
+        p_out, _ = p.communicate(timeout=60)
+    finally:
+        for proc in (p, d):
+            if proc.poll() is None:
+                proc.kill()
+    assert d.returncode == 0 and "decode ok" in d_out, d_out[-3000:]
+    assert p.returncode == 0 and "prefill ok" in p_out, p_out[-3000:]
