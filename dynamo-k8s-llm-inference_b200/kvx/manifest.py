@@ -32,6 +32,8 @@ class WorkerSpec:
     backend: str
     layout: int
     args: List[str] = field(default_factory=list)
+    bootstrap_port: Optional[int] = None   # --disaggregation-bootstrap-port (sglang/disagg.yaml:49-50,84-85)
+    transfer_backend: Optional[str] = None  # --disaggregation-transfer-backend (sglang/disagg.yaml:47-48: nixl)
 
 
 @dataclass
@@ -53,7 +55,8 @@ class Topology:
     def describe(self) -> Dict:
         return {"name": self.name, "backend": self.backend,
                 "workers": [{"name": w.name, "role": w.role, "replicas": w.replicas, "gpus": w.gpus, "tp": w.tp,
-                             "page_size": w.page_size, "model": w.model, "layout": "HND" if w.layout == HND else "NHD"}
+                             "page_size": w.page_size, "model": w.model, "layout": "HND" if w.layout == HND else "NHD",
+                             **({"bootstrap_port": w.bootstrap_port} if w.bootstrap_port else {})}
                             for w in self.workers]}
 
 
@@ -107,8 +110,10 @@ def parse_manifest(doc: Dict) -> Topology:
         tp = int(_arg_value(args, "--tp", "--tp-size", "--tensor-parallel-size", "-tp") or gpus)
         page = int(_arg_value(args, "--page-size", "--block-size") or 16)
         model = _arg_value(args, "--model", "--model-path", "--served-model-name")
+        port = _arg_value(args, "--disaggregation-bootstrap-port")
         workers.append(WorkerSpec(name, _role_of(svc, args), int(svc.get("replicas", 1)), gpus, tp, page, model, be,
-                                  BACKEND_LAYOUT[be], args))
+                                  BACKEND_LAYOUT[be], args, int(port) if port else None,
+                                  _arg_value(args, "--disaggregation-transfer-backend")))
     if not workers:
         raise ValueError("manifest declares no worker services")
     return Topology(str((doc.get("metadata") or {}).get("name", "dgd")), backend or "vllm", workers)

@@ -109,6 +109,10 @@ def test_reference_manifests_if_present():
         assert t.backend == be and t.disaggregated and t.gpus_needed() == 2
         assert all(w.replicas == 1 and w.gpus == 1 and w.tp == 1 and w.page_size == 16 for w in t.workers)
         assert not load_manifest(f"{base}/{be}/agg.yaml").disaggregated
+        if be == "sglang":   # the one manifest that names the handshake port and the transfer backend
+            assert {w.bootstrap_port for w in t.workers} == {12345} and {w.transfer_backend for w in t.workers} == {"nixl"}
+        else:
+            assert all(w.bootstrap_port is None for w in t.workers)
 
 
 def test_build_job_from_url(tmp_path):
