@@ -223,6 +223,7 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   // kvx_handoff_batch: (address, value) pairs the last CTA stores, carried next to the ids
   const uint64_t* notify = nullptr;
   uint32_t notify_count = 0;
+  bool block_major = false;  // visit items block by block (cross-layer pools)
 };
 
 // int32 entries of the parameter table area a launch needs: both sides' ids, then the notifications
@@ -428,6 +429,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   const Geometry g = resolve_geometry(ctx, remote, ls.src_is_peer, engine, ls.copy_mode, pl.piece_bytes);
   const uint32_t stages = g.stages, stage_bytes = g.stage_bytes, cons_warps = g.cons_warps;
   p.stages = stages; p.stage_bytes = stage_bytes;
+  p.block_major = (ls.block_major && !ls.copy_mode && env_or("KVX_BLOCK_MAJOR", 1) != 0) ? 1u : 0u;
   p.l2_hint = static_cast<uint32_t>(ctx->opt[KVX_OPT_L2_HINT]);
   p.flag = reinterpret_cast<unsigned long long*>(ls.flag);
   // Fence scopes (finish_and_flag): per CTA device-wide when the data stays on this GPU, and to the
@@ -644,6 +646,19 @@ int32_t unmap_ptr(kvx_ctx* ctx, void* ptr) {
   return KVX_OK;
 }
 
+// A cross-layer pool keeps every region of a block inside that block (region bases less than one block stride
+// apart, (nb, L, 2, N, H, D) or (nb, H, L, 2, N, D)): walking the items block by block then touches one
+// contiguous block of memory at a time instead of one chunk per block.
+bool regions_inside_one_block(const kvx_pool& pool) {
+  if (pool.base.size() < 2) return false;
+  uintptr_t lo = UINTPTR_MAX, hi = 0;
+  for (void* b : pool.base) {
+    lo = std::min(lo, reinterpret_cast<uintptr_t>(b));
+    hi = std::max(hi, reinterpret_cast<uintptr_t>(b));
+  }
+  return hi - lo < pool.desc.block_stride;
+}
+
 struct HostTables {
   const int32_t* src;
   const int32_t* dst;
@@ -676,6 +691,7 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.flag = flag;
   ls.flag_val = flag_val;
   ls.flag2 = flag2;
+  ls.block_major = regions_inside_one_block(*src) || regions_inside_one_block(*dst);
   ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
   ls.dst_is_peer_known = ls.dst_is_peer;
   ls.src_is_peer = !src->imported_ptrs.empty() || src->ctx != ctx;

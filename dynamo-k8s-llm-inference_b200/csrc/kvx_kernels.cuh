@@ -53,6 +53,7 @@ struct XferParams {
   // and lands at (x / d_n1) * d_stride_a + (x % d_n1) * d_stride_b.
   unsigned int d_runs, d_run_bytes, d_n1, d_stride_a, d_stride_b;
   unsigned int stages, stage_bytes;
+  unsigned int block_major;  // 1: items run block by block (all regions of block i, then block i+1) instead of region by region
   unsigned int l2_hint;
   unsigned int data_local;   // 1: every destination byte lands in THIS GPU's memory → a device-scope fence per CTA publishes it
   unsigned int flag_local;   // 1: the flag lives on this GPU too and nobody outside it observes it → device scope to the end
@@ -274,8 +275,13 @@ __device__ __forceinline__ void item_load(const XferParams& p, const Tab& tab, u
   raw.w = w;
   raw.piece = w % p.ppc;
   const unsigned c = w / p.ppc;
-  raw.i = c % p.n;
-  raw.r = c / p.n;
+  if (p.block_major) {  // cross-layer pools: a block's regions are adjacent in memory, visit them together
+    raw.r = c % p.regions;
+    raw.i = c / p.regions;
+  } else {
+    raw.i = c % p.n;
+    raw.r = c / p.n;
+  }
   side_load(p.src, tab, raw.r, raw.i, raw.s);
   side_load(p.dst, tab, raw.r, raw.i, raw.d);
 }
