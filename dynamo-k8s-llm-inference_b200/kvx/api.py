@@ -112,6 +112,12 @@ class Context:
             self.lib.kvx_ctx_destroy(self.handle)
             self.handle = None
 
+    def __enter__(self) -> "Context":
+        return self
+
+    def __exit__(self, *exc) -> None:
+        self.close()
+
     def set_option(self, name: str, value) -> None:
         if name == "engine" and isinstance(value, str):
             value = ENGINE[value]
