@@ -38,6 +38,7 @@ struct MemRecord {  // wire format of one exported device buffer
   uint64_t offset;  // raw_ptr - allocation base
   uint64_t bytes;
   cudaIpcMemHandle_t handle;
+  unsigned char device_uuid[16];  // the GPU the bytes live on: ordinals differ between processes, UUIDs do not
 };
 
 struct PoolRecordHeader {  // wire format of an exported pool: header + regions x MemRecord
@@ -71,7 +72,13 @@ struct kvx_ctx {
   cudaStream_t aux = nullptr;
   bool force_sys_fence = false;  // KVX_FORCE_SYS_FENCE=1: system-scope fences everywhere (debugging aid)
   std::string last_error;
-  std::map<void*, std::string> imported;  // imported pointer → handle key ("" = same process)
+  unsigned char uuid[16] = {0};  // this device's UUID
+  struct Imported {
+    std::string key;  // IPC handle bytes ("" = same process)
+    uint64_t bytes;
+    bool local;       // the memory lives on this context's GPU
+  };
+  std::map<void*, Imported> imported;  // pointers handed out by import_record
   std::map<const void*, size_t> smem_limit;  // kernel → dynamic shared memory limit already set
 };
 
@@ -82,6 +89,7 @@ struct kvx_pool {
   std::vector<void*> imported_ptrs;  // to unmap on release
   unsigned long long* d_bases = nullptr;
   uint64_t chunk_bytes = 0;
+  bool local = true;  // the pool's memory lives on the context's own GPU (whoever allocated or exported it)
 };
 
 namespace {
@@ -580,6 +588,7 @@ int32_t export_record(kvx_ctx* ctx, const void* ptr, uint64_t bytes, MemRecord* 
   rec->pid = static_cast<int64_t>(getpid());
   rec->raw_ptr = reinterpret_cast<uint64_t>(ptr);
   rec->bytes = bytes;
+  memcpy(rec->device_uuid, ctx->uuid, 16);  // exported memory is memory of this context's device
   uint64_t base = 0, size = 0;
   int32_t rc = alloc_base_of(ctx, ptr, &base, &size);
   if (rc) return rc;
@@ -594,9 +603,13 @@ int32_t export_record(kvx_ctx* ctx, const void* ptr, uint64_t bytes, MemRecord* 
   return KVX_OK;
 }
 
-int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out) {
+int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out, bool* local = nullptr) {
   if (rec->magic != kMemMagic) return KVX_EINVAL;
   DeviceGuard guard(ctx->device);
+  // cudaPointerGetAttributes reports the IMPORTING device for memory mapped through an IPC handle, so where the
+  // bytes live is taken from the exporter's record
+  const bool is_local = memcmp(rec->device_uuid, ctx->uuid, 16) == 0;
+  if (local) *local = is_local;
   if (rec->pid == static_cast<int64_t>(getpid())) {
     if (rec->device != ctx->device) {
       int can = 0;
@@ -607,7 +620,7 @@ int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out) {
       (void)cudaGetLastError();
     }
     *out = reinterpret_cast<void*>(rec->raw_ptr);
-    ctx->imported[*out] = std::string();
+    ctx->imported[*out] = kvx_ctx::Imported{std::string(), rec->bytes, is_local};
     return KVX_OK;
   }
   const std::string key(reinterpret_cast<const char*>(&rec->handle), sizeof(rec->handle));
@@ -626,14 +639,14 @@ int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out) {
     g_ipc_open[key] = IpcMapping{base, 1};
   }
   *out = static_cast<char*>(base) + rec->offset;
-  ctx->imported[*out] = key;
+  ctx->imported[*out] = kvx_ctx::Imported{key, rec->bytes, is_local};
   return KVX_OK;
 }
 
 int32_t unmap_ptr(kvx_ctx* ctx, void* ptr) {
   auto it = ctx->imported.find(ptr);
   if (it == ctx->imported.end()) return KVX_EINVAL;
-  const std::string key = it->second;
+  const std::string key = it->second.key;
   ctx->imported.erase(it);
   if (key.empty()) return KVX_OK;
   std::lock_guard<std::mutex> lk(g_ipc_mu);
@@ -644,6 +657,20 @@ int32_t unmap_ptr(kvx_ctx* ctx, void* ptr) {
     g_ipc_open.erase(m);
   }
   return KVX_OK;
+}
+
+// Does this address live on the context's own GPU?  Imported ranges answer from the exporter's record; for
+// memory allocated in this process the pointer attributes are reliable.
+bool pointer_is_local(kvx_ctx* ctx, const void* ptr) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(ptr);
+  for (const auto& kv : ctx->imported) {
+    const uintptr_t b = reinterpret_cast<uintptr_t>(kv.first);
+    if (a >= b && a < b + kv.second.bytes) return kv.second.local;
+  }
+  cudaPointerAttributes at{};
+  const bool remote = cudaPointerGetAttributes(&at, ptr) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->device;
+  (void)cudaGetLastError();
+  return !remote;
 }
 
 // A cross-layer pool keeps every region of a block inside that block (region bases less than one block stride
@@ -692,9 +719,9 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.flag_val = flag_val;
   ls.flag2 = flag2;
   ls.block_major = regions_inside_one_block(*src) || regions_inside_one_block(*dst);
-  ls.dst_is_peer = !dst->imported_ptrs.empty() || dst->ctx != ctx;
+  ls.dst_is_peer = !dst->local;
   ls.dst_is_peer_known = ls.dst_is_peer;
-  ls.src_is_peer = !src->imported_ptrs.empty() || src->ctx != ctx;
+  ls.src_is_peer = !src->local;
   if (ht) {
     ls.h_src_tab = ht->src; ls.h_dst_tab = ht->dst; ls.ns = ht->ns; ls.nd = ht->nd;
   }
@@ -748,6 +775,12 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) try {
   };
   if (!guard.ok) return fail(KVX_ECUDA);
   if (cudaDeviceGetAttribute(&ctx->sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return fail(KVX_ECUDA);
+  {
+    cudaDeviceProp prop{};
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return fail(KVX_ECUDA);
+    static_assert(sizeof(prop.uuid) == 16, "device UUID size");
+    memcpy(ctx->uuid, &prop.uuid, 16);
+  }
   if (cudaMalloc(&ctx->d_flags, kNumFlags * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ENOMEM);
   if (cudaMalloc(&ctx->d_counters, (kNumCounters + 1) * sizeof(unsigned)) != cudaSuccess) return fail(KVX_ENOMEM);
   if (cudaMalloc(&ctx->d_table_ring, static_cast<size_t>(kTableRing) * sizeof(int)) != cudaSuccess) return fail(KVX_ENOMEM);
@@ -896,6 +929,12 @@ int32_t kvx_pool_register(kvx_ctx* ctx, const kvx_pool_desc* desc, kvx_pool** ou
   kvx_pool* pool = new (std::nothrow) kvx_pool();
   if (!pool) return KVX_ENOMEM;
   pool->ctx = ctx;
+  {
+    // Where the bytes live decides the launch geometry and the fence scope, not how the pointer was obtained:
+    // a pool imported from another process on the SAME GPU is local memory, a peer's pool is not.
+    DeviceGuard g(ctx->device);
+    pool->local = pointer_is_local(ctx, desc->base[0]);
+  }
   pool->desc = *desc;
   pool->desc.block_stride = stride;
   pool->base.assign(desc->base, desc->base + desc->regions);
@@ -966,14 +1005,17 @@ int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** ou
   if (h.magic != kPoolMagic) return KVX_EINVAL;
   if (len < sizeof(h) + static_cast<size_t>(h.regions) * sizeof(MemRecord)) return KVX_EINVAL;
   std::vector<void*> bases(h.regions, nullptr);
+  bool all_local = true;
   const char* r = static_cast<const char*>(buf) + sizeof(h);
   int32_t rc = KVX_OK;
   uint32_t done = 0;
   for (; done < h.regions; ++done) {
     MemRecord rec;
     memcpy(&rec, r + done * sizeof(MemRecord), sizeof(rec));
-    rc = import_record(ctx, &rec, &bases[done]);
+    bool rec_local = true;
+    rc = import_record(ctx, &rec, &bases[done], &rec_local);
     if (rc) break;
+    all_local = all_local && rec_local;
   }
   if (rc) {
     for (uint32_t i = 0; i < done; ++i) unmap_ptr(ctx, bases[i]);
@@ -990,6 +1032,7 @@ int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** ou
     return rc;
   }
   pool->imported_ptrs = bases;
+  pool->local = all_local;  // from the exporter's records (pointer attributes cannot tell for IPC mappings)
   *out = pool;
   return KVX_OK;
 } KVX_CATCH_ALL
@@ -1060,6 +1103,7 @@ int32_t kvx_gather(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_table, ui
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
   ls.sg = ChunkGeom{d.layout, d.heads, so, d.block_tokens, d.head_stride};
   ls.dg = ChunkGeom{sl, hc, 0, d.block_tokens};
+  ls.src_is_peer = !src->local;
   return launch_xfer(ctx, ls, &src->base, nullptr, static_cast<cudaStream_t>(stream));
 } KVX_CATCH_ALL
 
@@ -1080,6 +1124,7 @@ int32_t kvx_scatter(kvx_ctx* ctx, const void* staging, const kvx_pool* dst, cons
   ls.N = d.block_tokens; ls.R = d.head_dim * d.elem_bytes; ls.Hc = hc;
   ls.sg = ChunkGeom{sl, hc, 0, d.block_tokens};
   ls.dg = ChunkGeom{d.layout, d.heads, dof, d.block_tokens, d.head_stride};
+  ls.dst_is_peer_known = !dst->local;
   return launch_xfer(ctx, ls, nullptr, &dst->base, static_cast<cudaStream_t>(stream));
 } KVX_CATCH_ALL
 
@@ -1098,12 +1143,8 @@ int32_t kvx_copy(kvx_ctx* ctx, const void* src, void* dst, uint64_t bytes, uint6
   ls.flag_val = flag_val;
   if (bytes != 0) {  // a side that lives on another GPU makes this an NVLink transfer (launch geometry only)
     DeviceGuard guard(ctx->device);
-    cudaPointerAttributes at{};
-    if (cudaPointerGetAttributes(&at, src) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->device)
-      ls.src_is_peer = true;
-    if (cudaPointerGetAttributes(&at, dst) == cudaSuccess && at.type == cudaMemoryTypeDevice && at.device != ctx->device)
-      ls.dst_is_peer_known = true;
-    (void)cudaGetLastError();
+    ls.src_is_peer = !pointer_is_local(ctx, src);
+    ls.dst_is_peer_known = !pointer_is_local(ctx, dst);
   }
   if (bytes == 0) {
     if (flag) return kvx_flag_reset(ctx, flag, flag_val, stream);

@@ -163,3 +163,14 @@ def test_runner_against_real_frontend(tmp_path, monkeypatch):
     finally:
         srv.shutdown()
         be.close()
+
+
+@pytest.mark.gpu
+def test_example_script_runs():
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "one_request.py")], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "prefill blocks released" in r.stdout, r.stdout + r.stderr
