@@ -3,8 +3,9 @@ external load generator (run-benchmarks.sh:56-68 → aiperf, not installable her
 OpenAI-compatible endpoint with the shape of the reference's own load script
 (examples/dgdr/trtllm/multi_convos_parallel.sh: NUM_CONVOS three-turn conversations, at most CONCURRENCY
 in flight, a conversation fails when any turn returns an error object; env knobs with the same names and
-defaults, :11-13) and records what the dashboard plots per request: latency (= time to first token for
-non-streamed replies) and, when the server reports it (`kvx.frontend` does), the KV-transfer time and bytes.
+defaults, :11-13) and records what the dashboard plots per request: time to first token (the first
+server-sent chunk with KVX_STREAM=1, else the whole reply) and, when the server reports it (`kvx.frontend`
+does, in non-streamed replies), the KV-transfer time and bytes.
 """
 from __future__ import annotations
 
@@ -25,13 +26,41 @@ def _endpoint(url: str) -> str:
     return u if u.endswith("/chat/completions") else (u + "/chat/completions" if u.endswith("/v1") else u + "/v1/chat/completions")
 
 
-def chat_once(endpoint: str, model: str, messages: List[Dict], timeout: float) -> Dict:
-    body = json.dumps({"model": model, "messages": messages, "temperature": 0, "max_tokens": 64}).encode()
+def _read_sse(r, t0: float) -> Dict:
+    """Server-sent events of a streamed completion: time to the first chunk, text of all chunks."""
+    first, text = None, []
+    for raw in r:
+        line = raw.decode("utf-8", "replace").strip()
+        if not line.startswith("data:"):
+            continue
+        data = line[5:].strip()
+        if first is None:
+            first = time.perf_counter() - t0
+        if data == "[DONE]":
+            break
+        try:
+            delta = json.loads(data)["choices"][0].get("delta", {})
+        except (ValueError, KeyError, IndexError):
+            return {"error": {"message": f"bad stream chunk: {data[:80]}"}}
+        text.append(delta.get("content") or "")
+    if first is None:
+        return {"error": {"message": "empty stream"}}
+    return {"choices": [{"message": {"role": "assistant", "content": "".join(text)}}], "_ttft_s": first}
+
+
+def chat_once(endpoint: str, model: str, messages: List[Dict], timeout: float, stream: bool = False) -> Dict:
+    payload = {"model": model, "messages": messages, "temperature": 0, "max_tokens": 64}
+    if stream:
+        payload["stream"] = True
+    body = json.dumps(payload).encode()
     req = urllib.request.Request(endpoint, body, {"Content-Type": "application/json"})
     t0 = time.perf_counter()
     try:
         with urllib.request.urlopen(req, timeout=timeout) as r:
-            resp = json.loads(r.read())
+            if stream and "text/event-stream" in (r.headers.get("Content-Type") or ""):
+                resp = _read_sse(r, t0)
+            else:
+                resp = json.loads(r.read())
     except urllib.error.HTTPError as e:
         try:
             resp = json.loads(e.read())
@@ -44,10 +73,11 @@ def chat_once(endpoint: str, model: str, messages: List[Dict], timeout: float) -
 
 
 def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None, concurrency: Optional[int] = None,
-                      prompt_tokens: Optional[int] = None, timeout: float = 60.0) -> Dict:
+                      prompt_tokens: Optional[int] = None, timeout: float = 60.0, stream: Optional[bool] = None) -> Dict:
     num_convos = int(os.environ.get("NUM_CONVOS", 10)) if num_convos is None else num_convos
     concurrency = int(os.environ.get("CONCURRENCY", 5)) if concurrency is None else concurrency
     prompt_tokens = int(os.environ.get("KVX_PROMPT_TOKENS", 1024)) if prompt_tokens is None else prompt_tokens
+    stream = (os.environ.get("KVX_STREAM", "0") not in ("", "0")) if stream is None else stream
     endpoint = _endpoint(url)
     sem = threading.Semaphore(max(1, concurrency))
     records: List[Dict] = []
@@ -61,7 +91,7 @@ def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None,
             ok = True
             for turn, text in enumerate(TURNS):
                 msgs.append({"role": "user", "content": text})
-                resp = chat_once(endpoint, model, msgs, timeout)
+                resp = chat_once(endpoint, model, msgs, timeout, stream)
                 if "error" in resp or not resp.get("choices"):
                     ok = False
                     rec = {"conversation": cid, "turn": turn, "error": str(resp.get("error", "no choices"))[:200],
@@ -70,6 +100,7 @@ def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None,
                     msgs.append({"role": "assistant", "content": resp["choices"][0]["message"]["content"]})
                     kt = resp.get("kv_transfer") or {}
                     rec = {"conversation": cid, "turn": turn, "latency_s": resp["_latency_s"],
+                           "ttft_s": resp.get("_ttft_s", resp["_latency_s"]),   # streamed: first chunk; else the whole reply
                            "prompt_tokens": (resp.get("usage") or {}).get("prompt_tokens"),
                            "xfer_time_seconds": kt.get("xfer_time_seconds"), "bytes_transferred": kt.get("bytes_transferred")}
                 with lock:
@@ -88,7 +119,7 @@ def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None,
         t.join()
     wall = time.perf_counter() - t0
     good = [r for r in records if "error" not in r]
-    lat = sorted(r["latency_s"] for r in good)
+    lat = sorted(r["ttft_s"] for r in good)
     xfer = [r for r in good if r.get("xfer_time_seconds")]
 
     def pct(v, p):
@@ -96,7 +127,7 @@ def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None,
 
     summary = {
         "endpoint": endpoint, "model": model, "conversations": num_convos, "concurrency": concurrency, "turns_per_conversation": len(TURNS),
-        "requests": len(records), "failed_conversations": sorted(failed), "wall_seconds": wall,
+        "requests": len(records), "failed_conversations": sorted(failed), "wall_seconds": wall, "streamed": bool(stream),
         "requests_per_second": len(good) / wall if wall > 0 else None,
         "time_to_first_token_seconds": {"p50": pct(lat, 0.5), "p90": pct(lat, 0.9), "max": lat[-1] if lat else None,
                                         "mean": statistics.mean(lat) if lat else None},

@@ -174,3 +174,18 @@ def test_example_script_runs():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     r = subprocess.run([sys.executable, os.path.join(root, "examples", "one_request.py")], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "prefill blocks released" in r.stdout, r.stdout + r.stderr
+
+
+def test_runner_streams_for_ttft(server, tmp_path, monkeypatch):
+    """KVX_STREAM=1: the load asks for server-sent events and takes time-to-first-token from the first chunk."""
+    import os
+
+    from kvx import cli
+
+    base, be = server
+    for k, v in (("NUM_CONVOS", "2"), ("CONCURRENCY", "2"), ("KVX_PROMPT_TOKENS", "32"), ("KVX_STREAM", "1")):
+        monkeypatch.setenv(k, v)
+    assert cli.main(["-u", base, "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "sse"]) == 0
+    res = json.load(open(os.path.join(tmp_path, "sse", "results.json")))
+    assert res["summary"]["streamed"] and res["summary"]["requests"] == 6 and not res["summary"]["failed_conversations"]
+    assert all(0 < r["ttft_s"] <= r["latency_s"] for r in res["requests"])
