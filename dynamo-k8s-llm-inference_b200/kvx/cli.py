@@ -111,6 +111,11 @@ def main(argv: Optional[List[str]] = None) -> int:
         os.makedirs(out_dir, exist_ok=True)
         summary = run_http_benchmark(url, model, os.path.join(out_dir, name))
         print(json.dumps(summary))
+        if plots:
+            from .plot import plot_dir
+
+            for p in plot_dir(out_dir):
+                print(f"plot: {p}")
         return 1 if (summary["failed_conversations"] or not summary["requests"]) else 0
     try:
         topo, cfg = build_job(url, model)

@@ -41,6 +41,15 @@ def plot_dir(data_dir: str) -> List[str]:
         if "results.json" not in files:
             continue
         res = json.load(open(os.path.join(root, "results.json")))
+        if "decode_ranks" not in res:  # an HTTP run (kvx/httpload.py): time to first token against the prompt length
+            pts = [(q["prompt_tokens"], 1e3 * q["ttft_s"]) for q in res.get("requests", []) if q.get("prompt_tokens") and "ttft_s" in q]
+            if pts:
+                path = os.path.join(root, "time_to_first_token_ms.svg")
+                with open(path, "w") as f:
+                    f.write(_svg_scatter(pts, f"{res['summary'].get('endpoint', 'endpoint')}: time to first token",
+                                         "prompt tokens", "time to first token (ms)"))
+                written.append(path)
+            continue
         reqs = [q for r in res["decode_ranks"] for q in r["requests"]]
         thr = [(q["isl"], q["throughput_GBps"]) for q in reqs]
         ttft = [(q["isl"], q["time_to_first_token_added_ms"]) for q in reqs]

@@ -185,7 +185,8 @@ def test_runner_streams_for_ttft(server, tmp_path, monkeypatch):
     base, be = server
     for k, v in (("NUM_CONVOS", "2"), ("CONCURRENCY", "2"), ("KVX_PROMPT_TOKENS", "32"), ("KVX_STREAM", "1")):
         monkeypatch.setenv(k, v)
-    assert cli.main(["-u", base, "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "sse"]) == 0
+    assert cli.main(["-u", base, "-m", "Qwen/Qwen3-0.6B", "-o", str(tmp_path), "-b", "sse", "-p"]) == 0
+    assert os.path.exists(os.path.join(tmp_path, "sse", "time_to_first_token_ms.svg"))
     res = json.load(open(os.path.join(tmp_path, "sse", "results.json")))
     assert res["summary"]["streamed"] and res["summary"]["requests"] == 6 and not res["summary"]["failed_conversations"]
     assert all(0 < r["ttft_s"] <= r["latency_s"] for r in res["requests"])
