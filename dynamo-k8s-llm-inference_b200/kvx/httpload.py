@@ -101,7 +101,9 @@ def run_conversations(url: str, model: str, *, num_convos: Optional[int] = None,
                     kt = resp.get("kv_transfer") or {}
                     rec = {"conversation": cid, "turn": turn, "latency_s": resp["_latency_s"],
                            "ttft_s": resp.get("_ttft_s", resp["_latency_s"]),   # streamed: first chunk; else the whole reply
-                           "prompt_tokens": (resp.get("usage") or {}).get("prompt_tokens"),
+                           # the server's count when it reports one, else the same estimate kvx.frontend uses
+                           "prompt_tokens": (resp.get("usage") or {}).get("prompt_tokens") or
+                                            max(1, sum(len(str(m.get("content", ""))) + 4 for m in msgs[:-1]) // 4),
                            "xfer_time_seconds": kt.get("xfer_time_seconds"), "bytes_transferred": kt.get("bytes_transferred")}
                 with lock:
                     records.append(rec)
