@@ -23,8 +23,16 @@ using kvx::XferSide;
 
 namespace {
 
-constexpr uint32_t kNumFlags = 4096;     // completion flags per context (uint64 each)
-constexpr uint32_t kNumCounters = 1024;  // done-counter ring (one per launch that carries a flag)
+constexpr uint32_t kNumFlags = 4096;     // completion flags per context (uint64 each), all visible to peers
+constexpr uint32_t kPrivFlags = 64;      // private words behind them (never exported): kvx_handoff_host's pageable h_done
+// Finished-CTA counters.  A counter is only touched while its kernel RUNS (one atomicAdd per CTA at the end, reset
+// by the last CTA), and kernels issued to one stream run one after the other — a dependent launch waits for its
+// predecessor's completion before its first global access — so two counters per stream, used alternately, can
+// never be shared by two running kernels however deep the backlog.  Launches recorded into a CUDA graph may be
+// replayed on any stream later, so each gets a counter of its own for the life of the context.
+constexpr uint32_t kStreamSlots = 448;   // distinct streams with flagged launches per context (2 counters each)
+constexpr uint32_t kGraphCounters = 128; // flagged launches recorded into CUDA graphs per context
+constexpr uint32_t kNumCounters = 2 * kStreamSlots + kGraphCounters;
 constexpr uint32_t kTableRing = 1u << 22;  // int32 entries of device scratch for host block tables
 constexpr uint64_t kNvlinkInFlightBytes = 8ull << 20;  // 6 MiB in flight saturate one NVLink direction (tools/footprint.py); margin for a busy switch
 constexpr uint32_t kMemMagic = 0x4d58564bu;   // "KVXM"
@@ -39,7 +47,10 @@ struct MemRecord {  // wire format of one exported device buffer
   uint64_t bytes;
   cudaIpcMemHandle_t handle;
   unsigned char device_uuid[16];  // the GPU the bytes live on: ordinals differ between processes, UUIDs do not
+  uint32_t flags;                 // kMemHasIpcHandle: `handle` can be opened by another process
+  uint32_t reserved;
 };
+constexpr uint32_t kMemHasIpcHandle = 1u;
 
 struct PoolRecordHeader {  // wire format of an exported pool: header + regions x MemRecord
   uint32_t magic;
@@ -55,6 +66,9 @@ struct IpcMapping {
 };
 std::mutex g_ipc_mu;
 std::map<std::string, IpcMapping> g_ipc_open;
+// A kernel's dynamic shared-memory limit is per process and device: every path that raises it (contexts on any
+// host thread, kvx_handoff_static's set-up) reads and writes it under this one lock, so "raise, never lower" holds.
+std::mutex g_func_attr_mu;
 
 }  // namespace
 
@@ -67,8 +81,17 @@ struct kvx_ctx {
   unsigned* d_counters = nullptr;
   unsigned* d_status = nullptr;
   int* d_table_ring = nullptr;
-  uint32_t counter_cursor = 0;
+  int* h_table_ring = nullptr;  // pinned mirror of d_table_ring, allocated on first use (long block-id lists only)
   uint32_t table_cursor = 0;
+  struct RingUse {  // a span of the table ring and the event that marks its reader's completion
+    uint32_t begin, end;
+    cudaEvent_t done;
+  };
+  std::vector<RingUse> ring_uses;
+  std::map<cudaStream_t, uint32_t> stream_slot;  // stream → its pair of counters
+  std::vector<uint8_t> slot_phase;               // which counter of the pair the stream's next launch takes
+  uint32_t graph_counters = 0;                   // counters handed to launches recorded into graphs
+  uint32_t priv_cursor = 0;
   cudaStream_t aux = nullptr;
   bool force_sys_fence = false;  // KVX_FORCE_SYS_FENCE=1: system-scope fences everywhere (debugging aid)
   std::string last_error;
@@ -264,6 +287,7 @@ template <typename K>
 int32_t set_smem(kvx_ctx* ctx, K kernel, size_t bytes) {
   size_t& have = ctx->smem_limit[reinterpret_cast<const void*>(kernel)];
   if (have >= bytes) return KVX_OK;
+  std::lock_guard<std::mutex> lk(g_func_attr_mu);
   cudaFuncAttributes fa{};
   KVX_CUDA(ctx, cudaFuncGetAttributes(&fa, kernel));  // another context or kvx_handoff_static may have raised it already
   if (static_cast<size_t>(fa.maxDynamicSharedSizeBytes) >= bytes) {
@@ -292,6 +316,38 @@ cudaError_t launch_kernel(K kernel, uint32_t grid, uint32_t block, size_t smem, 
   cfg.attrs = attr;
   cfg.numAttrs = pdl ? 1u : 0u;
   return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
+// The finished-CTA counter of one flagged launch (see kStreamSlots above).
+int32_t take_counter(kvx_ctx* ctx, cudaStream_t stream, unsigned** out) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess) {
+    (void)cudaGetLastError();
+    cs = cudaStreamCaptureStatusNone;
+  }
+  if (cs == cudaStreamCaptureStatusActive) {
+    if (ctx->graph_counters == kGraphCounters) {
+      ctx->last_error = "more than 128 flagged transfers recorded into CUDA graphs by one context";
+      return KVX_ERANGE;
+    }
+    *out = ctx->d_counters + 2 * kStreamSlots + ctx->graph_counters++;
+    return KVX_OK;
+  }
+  auto it = ctx->stream_slot.find(stream);
+  if (it == ctx->stream_slot.end()) {
+    if (ctx->stream_slot.size() == kStreamSlots) {
+      // Every pair is taken by a stream seen earlier (an engine that keeps creating streams): once the device
+      // is idle no counter is in use and all of them can be handed out again.
+      KVX_CUDA(ctx, cudaDeviceSynchronize());
+      ctx->stream_slot.clear();
+    }
+    if (ctx->slot_phase.size() != kStreamSlots) ctx->slot_phase.assign(kStreamSlots, 0);
+    // after a clear() the pairs are reassigned from 0 upwards
+    it = ctx->stream_slot.emplace(stream, static_cast<uint32_t>(ctx->stream_slot.size())).first;
+  }
+  const uint32_t slot = it->second;
+  *out = ctx->d_counters + 2 * slot + (ctx->slot_phase[slot] ^= 1u);
+  return KVX_OK;
 }
 
 // ---- launch geometry ----------------------------------------------------------------------------
@@ -445,10 +501,13 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.flag2 = reinterpret_cast<unsigned long long*>(ls.flag2);
   p.data_local = (!ls.dst_is_peer && !ctx->force_sys_fence) ? 1u : 0u;
   p.flag_local = (p.data_local && ls.flag2 == nullptr && ls.notify_count == 0 &&
-                  (ls.flag == nullptr || (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags))) ? 1u : 0u;
+                  (ls.flag == nullptr || (ls.flag >= ctx->d_flags && ls.flag < ctx->d_flags + kNumFlags + kPrivFlags))) ? 1u : 0u;
   p.flag_val = ls.flag_val;
   p.status = ctx->d_status;
-  p.done_counter = ctx->d_counters + (ctx->counter_cursor++ % kNumCounters);
+  if (ls.flag != nullptr || ls.flag2 != nullptr || ls.notify_count != 0) {  // only flagged launches count their CTAs
+    int32_t rc = take_counter(ctx, stream, &p.done_counter);
+    if (rc) return rc;
+  }
 
   // 32-byte accesses need every address component 32-byte aligned (region bases included).
   bool ok32 = all_aligned(32, pl, p.src, p.dst);
@@ -595,8 +654,11 @@ int32_t export_record(kvx_ctx* ctx, const void* ptr, uint64_t bytes, MemRecord* 
   rec->offset = rec->raw_ptr - base;
   if (rec->offset + bytes > size) return KVX_EINVAL;
   cudaError_t e = cudaIpcGetMemHandle(&rec->handle, reinterpret_cast<void*>(base));
-  if (e != cudaSuccess) {
-    // Not exportable (e.g. not a cudaMalloc allocation): still usable inside this process.
+  if (e == cudaSuccess) {
+    rec->flags |= kMemHasIpcHandle;
+  } else {
+    // Not a cudaMalloc allocation (VMM / expandable segments, a memory pool): the record still serves a context
+    // in THIS process, and says so — another process gets KVX_EIPC with this reason instead of a zero handle.
     (void)cudaGetLastError();
     memset(&rec->handle, 0, sizeof(rec->handle));
   }
@@ -622,6 +684,11 @@ int32_t import_record(kvx_ctx* ctx, const MemRecord* rec, void** out, bool* loca
     *out = reinterpret_cast<void*>(rec->raw_ptr);
     ctx->imported[*out] = kvx_ctx::Imported{std::string(), rec->bytes, is_local};
     return KVX_OK;
+  }
+  if (!(rec->flags & kMemHasIpcHandle)) {
+    ctx->last_error = "the exporter's memory has no CUDA IPC handle (not a plain cudaMalloc allocation): allocate the "
+                      "pool with kvx_mem_alloc / cudaMalloc, or switch off expandable segments";
+    return KVX_EIPC;
   }
   const std::string key(reinterpret_cast<const char*>(&rec->handle), sizeof(rec->handle));
   std::lock_guard<std::mutex> lk(g_ipc_mu);
@@ -695,6 +762,52 @@ struct NotifyList {
   const uint64_t* pairs;  // (address, value) x count
   uint32_t count;
 };
+
+// ---- table ring: device scratch (+ pinned mirror) for block-id lists too long for the parameter block ----------
+// Spans are handed out front to back and wrap; each span in use is remembered with an event recorded behind the
+// kernel that reads it, and a span overlapping it is not handed out before that event has fired.
+int32_t table_ring_take(kvx_ctx* ctx, uint32_t entries, uint32_t* at) {
+  if (entries > kTableRing) return KVX_ERANGE;
+  if (!ctx->h_table_ring) {
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&ctx->h_table_ring), static_cast<size_t>(kTableRing) * sizeof(int),
+                                  cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      ctx->h_table_ring = nullptr;
+      return KVX_ENOMEM;
+    }
+  }
+  if (ctx->table_cursor + static_cast<uint64_t>(entries) > kTableRing) ctx->table_cursor = 0;
+  const uint32_t b = ctx->table_cursor, e = b + entries;
+  for (size_t i = 0; i < ctx->ring_uses.size();) {
+    kvx_ctx::RingUse& u = ctx->ring_uses[i];
+    const bool overlaps = u.begin < e && b < u.end;
+    if (overlaps || cudaEventQuery(u.done) == cudaSuccess) {
+      if (overlaps) KVX_CUDA(ctx, cudaEventSynchronize(u.done));
+      cudaEventDestroy(u.done);
+      ctx->ring_uses[i] = ctx->ring_uses.back();
+      ctx->ring_uses.pop_back();
+    } else {
+      (void)cudaGetLastError();  // cudaErrorNotReady is not an error here
+      ++i;
+    }
+  }
+  ctx->table_cursor = e;
+  *at = b;
+  return KVX_OK;
+}
+
+int32_t table_ring_mark(kvx_ctx* ctx, uint32_t at, uint32_t entries, cudaStream_t st) {
+  cudaEvent_t ev = nullptr;
+  KVX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  cudaError_t e = cudaEventRecord(ev, st);
+  if (e != cudaSuccess) {
+    cudaEventDestroy(ev);
+    return cuda_fail(ctx, e, "cudaEventRecord");
+  }
+  ctx->ring_uses.push_back(kvx_ctx::RingUse{at, at + entries, ev});
+  return KVX_OK;
+}
 
 // The fused handoff behind kvx_handoff_fused (device tables) and kvx_handoff_host (host tables `ht`,
 // tried first as kernel parameters; completion word `flag2`).
@@ -781,10 +894,10 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) try {
     static_assert(sizeof(prop.uuid) == 16, "device UUID size");
     memcpy(ctx->uuid, &prop.uuid, 16);
   }
-  if (cudaMalloc(&ctx->d_flags, kNumFlags * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ENOMEM);
+  if (cudaMalloc(&ctx->d_flags, (kNumFlags + kPrivFlags) * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ENOMEM);
   if (cudaMalloc(&ctx->d_counters, (kNumCounters + 1) * sizeof(unsigned)) != cudaSuccess) return fail(KVX_ENOMEM);
   if (cudaMalloc(&ctx->d_table_ring, static_cast<size_t>(kTableRing) * sizeof(int)) != cudaSuccess) return fail(KVX_ENOMEM);
-  if (cudaMemset(ctx->d_flags, 0, kNumFlags * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ECUDA);
+  if (cudaMemset(ctx->d_flags, 0, (kNumFlags + kPrivFlags) * sizeof(uint64_t)) != cudaSuccess) return fail(KVX_ECUDA);
   if (cudaMemset(ctx->d_counters, 0, (kNumCounters + 1) * sizeof(unsigned)) != cudaSuccess) return fail(KVX_ECUDA);
   ctx->d_status = ctx->d_counters + kNumCounters;
   if (cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking) != cudaSuccess) return fail(KVX_ECUDA);
@@ -815,6 +928,8 @@ int32_t kvx_ctx_destroy(kvx_ctx* ctx) try {
       cudaFree(ctx->d_flags);
       cudaFree(ctx->d_counters);
       cudaFree(ctx->d_table_ring);
+      for (auto& u : ctx->ring_uses) cudaEventDestroy(u.done);
+      if (ctx->h_table_ring) cudaFreeHost(ctx->h_table_ring);
       (void)cudaGetLastError();
     }
   }
@@ -995,6 +1110,18 @@ int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) try {
     memcpy(w + r * sizeof(MemRecord), &rec, sizeof(rec));
   }
   *len = need;
+  return KVX_OK;
+} KVX_CATCH_ALL
+
+int32_t kvx_pool_exportable(kvx_pool* pool, int32_t* across_processes) try {
+  if (!pool || !across_processes) return KVX_EINVAL;
+  *across_processes = 1;
+  for (void* b : pool->base) {
+    MemRecord rec;
+    int32_t rc = export_record(pool->ctx, b, 16, &rec);
+    if (rc) return rc;
+    if (!(rec.flags & kMemHasIpcHandle)) *across_processes = 0;
+  }
   return KVX_OK;
 } KVX_CATCH_ALL
 
@@ -1188,7 +1315,9 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
     else
       (void)cudaGetLastError();
   }
-  uint64_t* f = flag ? flag : ((h_done && !done_dev) ? ctx->d_flags + (kNumFlags - 1) : nullptr);
+  // a private word behind the exported flags (peers never see it), rotated so that calls on different streams
+  // do not share one
+  uint64_t* f = flag ? flag : ((h_done && !done_dev) ? ctx->d_flags + kNumFlags + (ctx->priv_cursor++ % kPrivFlags) : nullptr);
 
   int32_t rc = kNoParamTables;
   if (n != 0 && static_cast<int64_t>(ns) + nd <= std::min<int64_t>(kParamTabMax, ctx->opt[KVX_OPT_PARAM_TABLES])) {
@@ -1199,15 +1328,26 @@ int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src
   if (rc == kNoParamTables) {
     int* d_src = nullptr;
     int* d_dst = nullptr;
+    uint32_t at = 0;
     if (n != 0) {
-      if (ctx->table_cursor + static_cast<uint64_t>(ns) + nd > kTableRing) ctx->table_cursor = 0;
-      d_src = ctx->d_table_ring + ctx->table_cursor;
+      // Long lists (more than the parameter block holds) go through the table ring.  They are copied into the
+      // ring's pinned mirror HERE, so the caller may reuse its lists as soon as the call returns whatever kind
+      // of host memory they are in, and a span of the ring is handed out again only after the kernel that
+      // read it has finished (an event per span; waiting for it is the back-pressure of a very deep backlog).
+      rc = table_ring_take(ctx, ns + nd, &at);
+      if (rc) return rc;
+      memcpy(ctx->h_table_ring + at, h_src_table, ns * sizeof(int));
+      memcpy(ctx->h_table_ring + at + ns, h_dst_table, nd * sizeof(int));
+      d_src = ctx->d_table_ring + at;
       d_dst = d_src + ns;
-      ctx->table_cursor += ns + nd;
-      KVX_CUDA(ctx, cudaMemcpyAsync(d_src, h_src_table, ns * sizeof(int), cudaMemcpyHostToDevice, st));
-      KVX_CUDA(ctx, cudaMemcpyAsync(d_dst, h_dst_table, nd * sizeof(int), cudaMemcpyHostToDevice, st));
+      KVX_CUDA(ctx, cudaMemcpyAsync(d_src, ctx->h_table_ring + at, (static_cast<size_t>(ns) + nd) * sizeof(int),
+                                    cudaMemcpyHostToDevice, st));
     }
     rc = handoff_impl(ctx, src, d_src, dst, d_dst, n, xf, f, flag_val, stream, nullptr, nullptr, done_dev);
+    if (n != 0) {
+      const int32_t rc2 = table_ring_mark(ctx, at, ns + nd, st);
+      if (rc == KVX_OK) rc = rc2;
+    }
   }
   if (rc) return rc;
   if (h_done && !done_dev) {
@@ -1284,15 +1424,12 @@ int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst
 // =================================================================================================
 namespace {
 
-// Layout of the array, in bytes: [src region bases][dst region bases][src table][dst table][counter, status].
-constexpr size_t kStaticBasesBytes = static_cast<size_t>(KVX_STATIC_MAX_REGIONS) * sizeof(unsigned long long);
-constexpr size_t kStaticTableBytes = static_cast<size_t>(KVX_STATIC_MAX_BLOCKS) * sizeof(int);
-constexpr size_t kStaticOffSrcBases = 0;
-constexpr size_t kStaticOffDstBases = kStaticBasesBytes;
-constexpr size_t kStaticOffSrcTable = 2 * kStaticBasesBytes;
-constexpr size_t kStaticOffDstTable = kStaticOffSrcTable + kStaticTableBytes;
-constexpr size_t kStaticOffWords = kStaticOffDstTable + kStaticTableBytes;  // counter at +0, status at +4
-static_assert(kStaticOffWords + 256 == KVX_STATIC_SCRATCH_BYTES, "scratch layout and header limit disagree");
+// Layout of the array for one call, in bytes: [counter, status, padding: 256][src region bases][dst region bases]
+// [src table][dst table], packed for that call's region and block counts so that ONE upload carries everything.
+constexpr size_t kStaticWordsBytes = 256;  // counter at +0, status at +4
+static_assert(kStaticWordsBytes + 2 * static_cast<size_t>(KVX_STATIC_MAX_REGIONS) * sizeof(unsigned long long) +
+                      2 * static_cast<size_t>(KVX_STATIC_MAX_BLOCKS) * sizeof(int) == KVX_STATIC_SCRATCH_BYTES,
+              "scratch layout and header limit disagree");
 
 // In host code this name is only a handle for cudaGetSymbolAddress, never a device address.
 static __device__ __align__(256) unsigned char g_static_scratch[KVX_STATIC_SCRATCH_BYTES];
@@ -1307,13 +1444,18 @@ struct StaticDevice {
 };
 StaticDevice g_static_dev[kStaticMaxDevices];
 std::mutex g_static_mu;
+// Host-side image of the array for the call being issued (ordinary pageable memory, no allocation).  The caller's
+// lists and base addresses are copied and range-checked HERE, and the upload reads this copy: an H2D copy from
+// pageable memory has taken its source by the time cudaMemcpyAsync returns, so the caller's own buffers — pinned or
+// not — are free again on return, and the ids the kernel reads are exactly the ids that were checked.
+alignas(16) unsigned char g_static_stage[KVX_STATIC_SCRATCH_BYTES];
 
 // Once per device, with that device current: resolve the array's device address, size the kernel's
 // shared memory, read the SM count.  None of these calls allocates.
 int32_t static_setup(int device, StaticDevice** out) {
-  std::lock_guard<std::mutex> lk(g_static_mu);
-  StaticDevice& d = g_static_dev[device];
+  StaticDevice& d = g_static_dev[device];  // the caller holds g_static_mu
   if (!d.ready) {
+    std::lock_guard<std::mutex> attr_lk(g_func_attr_mu);
     void* ptr = nullptr;
     cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);
     if (e != cudaSuccess || ptr == nullptr) {
@@ -1375,10 +1517,6 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   if (!same_shape(*src, *dst)) return KVX_EINVAL;
   if (src->block_tokens != dst->block_tokens) return KVX_EUNSUPPORTED;  // no block-size regrouping here
   if (n != 0 && (!h_src_table || !h_dst_table)) return KVX_EINVAL;
-  for (uint32_t i = 0; i < n; ++i) {
-    if (h_src_table[i] < 0 || static_cast<uint64_t>(h_src_table[i]) >= src->num_blocks) return KVX_ERANGE;
-    if (h_dst_table[i] < 0 || static_cast<uint64_t>(h_dst_table[i]) >= dst->num_blocks) return KVX_ERANGE;
-  }
   uint32_t so, dof, hc, sl;
   rc = resolve_xform(src, dst, xf, &so, &dof, &hc, &sl, src->layout);
   if (rc) return rc;
@@ -1388,8 +1526,9 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
     (void)cudaGetLastError();
     return KVX_ECUDA;
   }
+  std::lock_guard<std::mutex> lk(g_static_mu);  // one host thread at a time builds and uploads the image
   StaticDevice* dev = nullptr;
-  rc = static_setup(device, &dev);  // first call on this device: do it before any stream capture
+  rc = static_setup(device, &dev);  // first call on this device: do it at start-up, before any stream capture
   if (rc) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   auto bad = [](cudaError_t e) {
@@ -1411,26 +1550,39 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   if (total >= (1ull << 31)) return KVX_EUNSUPPORTED;
 
   unsigned char* sc = dev->scratch;
-  // The array keeps whatever the previous call left: upload everything this launch reads and zero
-  // the counter and status word, all ordered on the caller's stream.
-  if (bad(cudaMemcpyAsync(sc + kStaticOffSrcBases, src->base, src->regions * sizeof(void*), cudaMemcpyHostToDevice, st)) ||
-      bad(cudaMemcpyAsync(sc + kStaticOffDstBases, dst->base, dst->regions * sizeof(void*), cudaMemcpyHostToDevice, st)) ||
-      bad(cudaMemcpyAsync(sc + kStaticOffSrcTable, h_src_table, n * sizeof(int), cudaMemcpyHostToDevice, st)) ||
-      bad(cudaMemcpyAsync(sc + kStaticOffDstTable, h_dst_table, n * sizeof(int), cudaMemcpyHostToDevice, st)) ||
-      bad(cudaMemsetAsync(sc + kStaticOffWords, 0, 256, st)))
-    return KVX_ECUDA;
+  const uint32_t regions = src->regions;  // == dst->regions (same_shape)
+  const size_t off_sbases = kStaticWordsBytes, off_dbases = off_sbases + regions * sizeof(unsigned long long);
+  const size_t off_stable = off_dbases + regions * sizeof(unsigned long long), off_dtable = off_stable + n * sizeof(int);
+  const size_t image_bytes = off_dtable + n * sizeof(int);
+  // The array keeps whatever the previous call left: build this call's image — zeroed counter and status word,
+  // base addresses, both tables — in host memory, check the ids on that copy, and upload it in one piece,
+  // ordered on the caller's stream.
+  memset(g_static_stage, 0, kStaticWordsBytes);
+  memcpy(g_static_stage + off_sbases, src->base, regions * sizeof(void*));
+  memcpy(g_static_stage + off_dbases, dst->base, regions * sizeof(void*));
+  memcpy(g_static_stage + off_stable, h_src_table, n * sizeof(int));
+  memcpy(g_static_stage + off_dtable, h_dst_table, n * sizeof(int));
+  {
+    const int* ts = reinterpret_cast<const int*>(g_static_stage + off_stable);
+    const int* td = reinterpret_cast<const int*>(g_static_stage + off_dtable);
+    for (uint32_t i = 0; i < n; ++i) {
+      if (ts[i] < 0 || static_cast<uint64_t>(ts[i]) >= src->num_blocks) return KVX_ERANGE;
+      if (td[i] < 0 || static_cast<uint64_t>(td[i]) >= dst->num_blocks) return KVX_ERANGE;
+    }
+  }
+  if (bad(cudaMemcpyAsync(sc, g_static_stage, image_bytes, cudaMemcpyHostToDevice, st))) return KVX_ECUDA;
 
   XferParams p{};
-  p.src.bases = reinterpret_cast<const unsigned long long*>(sc + kStaticOffSrcBases);
-  p.src.table = reinterpret_cast<const int*>(sc + kStaticOffSrcTable);
+  p.src.bases = reinterpret_cast<const unsigned long long*>(sc + off_sbases);
+  p.src.table = reinterpret_cast<const int*>(sc + off_stable);
   p.src.block_stride = s_stride;
   p.src.num_blocks = src->num_blocks;
   p.src.slice_off = pl.s_slice_off;
   p.src.piece_stride = pl.s_piece_stride;
   p.src.ratio = 1;
   p.dst.ratio = 1;
-  p.dst.bases = reinterpret_cast<const unsigned long long*>(sc + kStaticOffDstBases);
-  p.dst.table = reinterpret_cast<const int*>(sc + kStaticOffDstTable);
+  p.dst.bases = reinterpret_cast<const unsigned long long*>(sc + off_dbases);
+  p.dst.table = reinterpret_cast<const int*>(sc + off_dtable);
   p.dst.block_stride = d_stride;
   p.dst.num_blocks = dst->num_blocks;
   p.dst.slice_off = pl.d_slice_off;
@@ -1443,8 +1595,8 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   p.stages = kStaticStages; p.stage_bytes = kStaticStageBytes;
   p.flag = reinterpret_cast<unsigned long long*>(flag);
   p.flag_val = flag_val;
-  p.done_counter = reinterpret_cast<unsigned int*>(sc + kStaticOffWords);
-  p.status = reinterpret_cast<unsigned int*>(sc + kStaticOffWords + 4);
+  p.done_counter = reinterpret_cast<unsigned int*>(sc);
+  p.status = reinterpret_cast<unsigned int*>(sc + 4);
 
   const uint32_t grid = std::min<uint32_t>(static_cast<uint32_t>(dev->sms) * kStaticCtasPerSm, p.total_items);
   kvx::kvx_xfer_tma_kernel<16, 8><<<grid, 32u * (1u + kStaticConsumerWarps), kStaticStages * kStaticStageBytes, st>>>(p);

@@ -83,6 +83,12 @@ class Pool:
         self.ctx._check(self.ctx.lib.kvx_pool_export(self.handle, buf, ctypes.byref(need)), "kvx_pool_export")
         return buf.raw[: need.value]
 
+    @property
+    def exportable_across_processes(self) -> bool:
+        out = c_i32()
+        self.ctx._check(self.ctx.lib.kvx_pool_exportable(self.handle, ctypes.byref(out)), "kvx_pool_exportable")
+        return bool(out.value)
+
     def release(self) -> None:
         if self.handle:
             self.ctx.lib.kvx_pool_release(self.handle)

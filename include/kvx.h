@@ -154,9 +154,20 @@ int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes);
 /* = agent metadata + add_remote_agent: descriptor + peer handles of every region. */
 int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len);
 int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out);
+/* Can another PROCESS import this pool?  *across_processes = 1 when every region lies in a plain
+ * cudaMalloc allocation (CUDA IPC handle available), 0 for memory without one (VMM / expandable
+ * segments, stream-ordered pools): such a pool still exports to contexts of the same process, and
+ * kvx_pool_import in another process fails with KVX_EIPC and the reason in kvx_last_error().  The
+ * pods of the reference's manifests are separate processes (vllm/disagg.yaml:23-25,43-45), so a
+ * worker should check this once after registering its pool. */
+int32_t kvx_pool_exportable(kvx_pool* pool, int32_t* across_processes);
 
 /* Completion flags: an array of uint64 in this context's device memory that a peer may write
- * (= NIXL notifications, [vllm] worker.py:2164,1792-1845). */
+ * (= NIXL notifications, [vllm] worker.py:2164,1792-1845).
+ * Limits of flagged transfers (those given a flag, an h_done word or batch notifications): one
+ * context serves up to 448 distinct streams at a time (beyond that a call waits for the device to
+ * go idle once and starts over) and up to 128 flagged transfers recorded into CUDA graphs
+ * (KVX_ERANGE afterwards); the backlog on each stream is unbounded. */
 int32_t kvx_ctx_flags(kvx_ctx* ctx, uint64_t** flags, uint32_t* count);
 int32_t kvx_flag_reset(kvx_ctx* ctx, uint64_t* flag, uint64_t value, void* stream);
 /* Stream-ordered wait until *flag >= value (bounded: timeout_ms, then the context is marked failed
@@ -201,7 +212,9 @@ int32_t kvx_handoff_fused(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_sr
  * up to 64k tokens at 16-token blocks) travel in the kernel's parameter block — one launch, no copy
  * before it; longer ones are uploaded into context scratch first.  When `h_done` is not NULL it receives flag_val once every byte has landed: pinned
  * (cudaHostAlloc / cudaHostRegister) memory is written by the kernel itself, pageable memory by a
- * D2H copy queued behind it on the same stream.  The lists are consumed before the call returns.
+ * D2H copy queued behind it on the same stream.  The lists are consumed before the call returns,
+ * whatever kind of host memory they are in (long lists are copied into a pinned ring of the
+ * context first; a span of that ring is reused only after the kernel that read it has finished).
  * n is bounded by KVX_MAX_HOST_TABLE. */
 #define KVX_MAX_HOST_TABLE (1u << 20)
 int32_t kvx_handoff_host(kvx_ctx* ctx, const kvx_pool* src, const int32_t* h_src_table,
@@ -250,12 +263,19 @@ int32_t kvx_handoff_batch(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst
  * process exits).  The call performs no cudaMalloc, cudaFree or other allocating call.
  *
  * Limits: n <= KVX_STATIC_MAX_BLOCKS and src/dst regions <= KVX_STATIC_MAX_REGIONS, otherwise the
- * call returns KVX_ERANGE and launches nothing.  Block ids are checked against num_blocks
- * (KVX_ERANGE).  Tables are HOST pointers; `flag` (device memory, may be NULL) receives flag_val
- * when every byte has landed.
+ * call returns KVX_ERANGE and launches nothing.  Tables are HOST pointers; `flag` (device memory,
+ * may be NULL) receives flag_val when every byte has landed.
+ *
+ * Lifetime of the arguments: the block-id lists and both descriptors' base arrays are copied into
+ * a buffer inside the library before anything is queued, the ids are checked against num_blocks on
+ * that copy (KVX_ERANGE, nothing launched), and the upload reads that copy.  The caller may
+ * therefore reuse or free them — pinned or pageable — as soon as the call returns, and the kernel
+ * can never see an id that was not checked.
  *
  * One-time set-up: the first call on each device looks up the array's device address and prepares
- * the kernel.  Make that first call before starting any stream capture on that device.
+ * the kernel; loading the kernel image and the array may take device memory once.  Make that first
+ * call (n = 0 is enough) at start-up: before the KV pool claims the rest of HBM, and before
+ * starting any stream capture on that device.  Later calls leave free device memory unchanged.
  *
  * Sharing: every call on a device uses the same array, which still holds the previous call's
  * tables; the call re-uploads what it reads and clears the counter and status word itself.  Two

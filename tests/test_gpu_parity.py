@@ -467,6 +467,59 @@ def test_host_entry_table_transport(param_tables, n):
     c.close()
 
 
+@pytest.mark.parametrize("param_tables", [8000, 0], ids=["ptab", "upload"])
+def test_host_lists_are_consumed_on_return(param_tables):
+    """kvx.h: "the lists are consumed before the call returns" — also when they sit in PINNED memory, from which
+    a plain cudaMemcpyAsync would read them after the call has returned.  Several requests are queued behind a
+    long-running copy and each one's pinned lists are overwritten the moment its call returns."""
+    c = kvx.Context(0, param_tables=param_tables)
+    nb, n = 300, 64
+    src = o.make_pool(2, 8, 64, nb, o.HND, seed=3)
+    dst = o.make_pool(2, 8, 64, nb, o.NHD, fill="canary")
+    dsrc, ddst = DevPool(c, src), DevPool(c, dst)
+    perm_s, perm_d = o.make_table(nb, 4 * n, 21), o.make_table(nb, 4 * n, 22)
+    pin_s, pin_d = torch.zeros(n, dtype=torch.int32).pin_memory(), torch.zeros(n, dtype=torch.int32).pin_memory()
+    big_a = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    big_b = torch.empty_like(big_a)
+    for _ in range(4):  # keep the stream busy so that the handoffs below are still queued when their calls return
+        big_b.copy_(big_a)
+    for k in range(4):
+        pin_s.copy_(torch.from_numpy(perm_s[k * n:(k + 1) * n]))
+        pin_d.copy_(torch.from_numpy(perm_d[k * n:(k + 1) * n]))
+        c.handoff_host(dsrc.kp, pin_s, ddst.kp, pin_d, n)
+        pin_s.fill_(1); pin_d.fill_(1)   # valid ids, wrong blocks: a late read would move block 1 onto block 1
+        o.handoff(src, perm_s[k * n:(k + 1) * n], dst, perm_d[k * n:(k + 1) * n])
+    torch.cuda.synchronize()
+    assert np.array_equal(ddst.bytes(), dst.buf)
+    c.check()
+    c.close()
+
+
+def test_table_ring_wraps_under_backlog():
+    """Lists too long for the parameter block travel through the context's table ring (4 Mi entries).  Spans are
+    reused only after their reader has finished: 12 requests of 2 x 400k ids wrap the ring twice while earlier ones
+    are still queued, and every one must move exactly its own blocks."""
+    c = kvx.Context(0)
+    nb, n = 400_001, 400_000
+    src = o.make_pool(1, 1, 8, nb, o.NHD, seed=9, block_tokens=1)     # 16-byte chunks: a big table, few bytes
+    dst = o.make_pool(1, 1, 8, nb, o.NHD, fill="canary", block_tokens=1)
+    dsrc, ddst = DevPool(c, src), DevPool(c, dst)
+    big_a = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    big_b = torch.empty_like(big_a)
+    for _ in range(4):
+        big_b.copy_(big_a)
+    want = dst.buf.copy()
+    sv, wv = src.buf.view(np.uint8).reshape(2, nb, 16), want.view(np.uint8).reshape(2, nb, 16)  # [K|V][block][chunk]
+    for k in range(12):
+        ts, td = o.make_table(nb, n, 100 + k), o.make_table(nb, n, 200 + k)
+        c.handoff_host(dsrc.kp, ts, ddst.kp, td, n)
+        wv[:, td] = sv[:, ts]
+    torch.cuda.synchronize()
+    assert np.array_equal(ddst.bytes(), want.view(np.uint8).reshape(-1))
+    c.check()
+    c.close()
+
+
 def _cross_layer_nhd_pool(L, H, D, nb, fill, seed=0, N=16, E=2):
     """vLLM's cross-layer block pool in NHD order: one allocation (num_blocks, num_layers, 2, N, H, D)
     ([vllm] v1/attention/backends/flash_attn.py:158-160).  As a kvx pool: region (l, kv) starts at

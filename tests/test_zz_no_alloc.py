@@ -52,11 +52,23 @@ def test_static_entry_matches_host_entry_twice():
         (o.make_table(nb, 150, 1), o.make_table(nb, 150, 2), None),
         (o.make_table(nb, 37, 3), o.make_table(nb, 37, 4), kvx.Xform(2, 4, 3, kvx.NHD)),
     ]
+    # The first call on a device does the one-time set-up (it may load the kernel image); from then on a call
+    # must leave free device memory exactly as it found it — that is what "allocates nothing" means to an engine
+    # that has budgeted every byte.  n = 0 is the start-up call the header recommends.
+    assert api.handoff_static(0, d_src, None, d_new, None, 0) == 0
+    torch.cuda.synchronize()
     for i, (ts, td, xf) in enumerate(calls):
         ctx.handoff_host(p_src, ts, p_ref, td, len(ts), xf, flag_val=i + 1)
-        rc = api.handoff_static(0, d_src, ts, d_new, td, len(ts), xf, flag=flag.data_ptr() + 8, flag_val=10 + i)
+        torch.cuda.synchronize()
+        # block-id lists in PINNED memory, overwritten as soon as the call returns: the call must have taken them
+        pin_s, pin_d = torch.from_numpy(ts.copy()).pin_memory(), torch.from_numpy(td.copy()).pin_memory()
+        free_before, _ = torch.cuda.mem_get_info()
+        rc = api.handoff_static(0, d_src, pin_s, d_new, pin_d, len(ts), xf, flag=flag.data_ptr() + 8, flag_val=10 + i)
+        pin_s.zero_(); pin_d.zero_()
         assert rc == 0, rc
         torch.cuda.synchronize()
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before, f"call {i + 1} changed free device memory by {free_before - free_after} bytes"
         assert torch.equal(t_new, t_ref), f"call {i + 1}: static entry differs from kvx_handoff_host"
         assert int(flag[1]) == 10 + i
     # and both equal the oracle
