@@ -32,7 +32,9 @@ for _p in (ROOT, PKG):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
-METRIC = "kv_transfer_GBps_per_PD_pair"
+# BASELINE.json's metric is per P->D pair; the bench contract wants the whole job in `value`, so the line carries the
+# sum over the concurrent pairs under this name and the per-pair figure next to it (`per_pair_GBps`).
+METRIC = "kv_transfer_GBps_sum_over_PD_pairs"
 UNIT = "GB/s"
 
 
@@ -177,8 +179,8 @@ def workload_config(n_gpus, shape, isl):
     if n_gpus == 1:
         wl = f"config#2 {shape.name} KV shape, single-GPU intra-device handoff HND->NHD, ISL {isl}"
     else:
-        wl = (f"config#{3 if n_gpus == 2 else 5} {shape.name} KV shape, {n_gpus // 2}P{n_gpus // 2}D over NVLink, "
-              f"HND->NHD, ISL {isl}")
+        wl = (f"{shape.name} KV shape, {n_gpus // 2}P{n_gpus // 2}D over NVLink, HND->NHD, fixed ISL {isl} "
+              f"({'config#3 topology' if n_gpus == 2 else 'config#5 topology; its mixed-ISL stream is the config5_mixed_isl block'})")
     return {"workload": wl, "layers": shape.layers, "kv_heads": shape.kv_heads, "head_dim": shape.head_dim,
             "block_tokens": shape.block_tokens, "isl": isl, "pairs": max(1, n_gpus // 2),
             "l2": "each request's payload (>= 896 MiB) exceeds the 126 MB L2 and steps rotate over 4 disjoint block sets"}
@@ -468,13 +470,59 @@ def run_single(args):
     return 0
 
 
+def pull_ncu_traffic():
+    """Local DRAM bytes of one 1 GiB pull from the committed ncu capture (the payload arrives over NVLink and is
+    written once to local HBM; nvlrx/nvltx counters read 0 on this driver)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01s2_ncu_pull_summary.json")) as f:
+            d = json.load(f)
+        return int(d["launches"][0]["dram_traffic_bytes"]), d.get("report")
+    except Exception:
+        return None, None
+
+
+def harness_leg(dist, rank, world, topo, cfg, group_ranks=None):
+    """One verified request stream through kvx.harness.run_rank on the ranks torchrun started (the same code
+    `run-benchmarks.sh -u kvx://...` runs in processes of its own).  Ranks outside `group_ranks` sit it out."""
+    from kvx import harness
+
+    plans = harness.rank_plans(topo, world)
+    group = None
+    if group_ranks is not None and len(group_ranks) != world:
+        group = dist.new_group(ranks=group_ranks, backend="gloo")  # collective: every rank creates it
+    summary = None
+    if group_ranks is None or rank in group_ranks:
+        res = harness.run_rank(rank, plans, cfg, group=group)
+        if rank == 0:
+            summary = harness.summarize(res["all"], topo.describe(), cfg, len(plans), world)
+    dist.barrier()
+    return summary
+
+
+def brief(summary, extra=()):
+    """The part of a harness summary that belongs in the bench line."""
+    if summary is None:
+        return None
+    keys = ("requests", "concurrency", "route", "aggregate_throughput_GBps", "per_request_throughput_GBps_median",
+            "per_edge_throughput_GBps_median", "per_decode_rank_ingress_GBps", "pct_of_nvlink_900", "per_isl",
+            "time_to_first_token_added_ms", "xfer_time_seconds", "verified_bit_exact", "requests_verified",
+            "blocks_checked", "canary_blocks_checked", "prefill_blocks_released", "releases_observed", "wall_seconds") + tuple(extra)
+    out = {k: summary[k] for k in keys if k in summary}
+    for k, v in list(out.items()):
+        if isinstance(v, float):
+            out[k] = round(v, 3)
+    out["topology"] = summary["topology"]["name"]
+    return out
+
+
 def run_pairs(args):
     import numpy as np
     import torch
     import torch.distributed as dist
 
     import kvx
-    from kvx import synth
+    from kvx import harness, synth
+    from kvx.manifest import synthetic_topology
     from kvx.workers import DecodeWorker, PrefillWorker
 
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
@@ -505,8 +553,8 @@ def run_pairs(args):
     else:
         w = DecodeWorker(local, shape, nb, kvx.NHD, seed=rank)
         synth.fill_canary(w.kv)
-    w.expect(0)
-    w.expect(1)
+    for slot in range(4):
+        w.expect(slot)
     torch.cuda.synchronize()
     metas = [None] * world
     dist.all_gather_object(metas, w.metadata())
@@ -523,6 +571,14 @@ def run_pairs(args):
     pull = args.mode == "pull"
     clocks = None
     mover = (not is_p) if pull else is_p  # the rank whose GPU runs the transfer kernel
+    alone_steps = min(args.steps, 20)
+    # block sets this rank's pool takes part in: warm-up + timed steps, the e2e steps, the one-pair run (pair 0), and —
+    # with the extras — the staged path's five scatters and the CPU-staged request (set 0)
+    used_sets = {k % sets for k in range(total_steps)} | {k % sets for k in range(args.steps)}
+    if rank in (0, pairs):
+        used_sets |= {k % sets for k in range(alone_steps)}
+    if not args.no_extras:
+        used_sets |= {r % sets for r in range(5)} | {0}
 
     def move(k, slot, value, host, h_done=None):
         s = k % sets
@@ -532,11 +588,13 @@ def run_pairs(args):
         else:
             w.push(0, src, dst, slot=slot, value=value, host_tables=host, h_done=h_done, stream=stream)
 
-    def step(k):
+    def step(k, slot=0, base=0, active=True):
+        if not active:
+            return
         if mover:
-            move(k, 0, k + 1, False)
+            move(k, slot, base + k + 1, False)
         else:  # the other side only learns about completion through its flag
-            w.wait(0, k + 1, 10000, stream)
+            w.wait(slot, base + k + 1, 10000, stream)
 
     torch.cuda.synchronize()
     dist.barrier()
@@ -575,9 +633,21 @@ def run_pairs(args):
     if rank == 0:
         clocks = sampler.stop()
 
+    # pair 0 alone (the other pairs idle): what the concurrent pairs cost each other
+    active = rank in (0, pairs)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms_alone = timed_loop(torch, stream, lambda k: step(k, slot=3, base=0, active=active), alone_steps) if active else 0.0
+    torch.cuda.synchronize()
+    dist.barrier()
+
     # the unfused path of the same request: gather (P GPU) -> copy over NVLink (D GPU pulls the staging
-    # image) -> scatter (D GPU), each kernel timed on its own GPU
-    staged = None
+    # image) -> scatter (D GPU), each kernel timed on its own GPU; next to it the library yardstick for the copy
+    # (the copy engines moving the same image: cudaMemcpyAsync between the two GPUs' memories = cudaMemcpyPeerAsync)
+    # and the CPU-staged handoff (D2H of the request's blocks into pinned host memory -> host
+    # memcpy-per-row transform -> H2D -> scatter)
+    staged, baselines = None, None
+    threads = len(os.sched_getaffinity(0))
     if not args.no_extras:
         reps = 5
         st_ptr = w.ctx.mem_alloc(payload)
@@ -585,11 +655,13 @@ def run_pairs(args):
         dist.all_gather_object(blobs, w.ctx.mem_export(st_ptr, payload) if is_p else None)
         tiny = torch.zeros(64, dtype=torch.uint8, device="cuda")
         xf = kvx.Xform(0, 0, 0, kvx.NHD)
-        w.expect(2)
+        xf_raw = kvx.Xform(0, 0, 0, kvx.HND)   # CPU-staged leg: the image leaves the prefill GPU untransformed
         torch.cuda.synchronize()
         dist.barrier()
-        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(reps)]
+        evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(reps)]
         peer_stage = None if is_p else w.ctx.mem_import(blobs[peer])
+        mine_t = synth.as_torch(st_ptr, payload, local)
+        peer_t = None if is_p else synth.as_torch(peer_stage, payload, local)
         for r in range(reps):
             if is_p:
                 evs[r][0].record(stream)
@@ -600,8 +672,10 @@ def run_pairs(args):
             else:
                 w.wait(2, r + 1, 10000, stream)
                 evs[r][0].record(stream)
-                w.ctx.copy(peer_stage, st_ptr, payload, None, 0, stream)                    # NVLink read
+                w.ctx.copy(peer_stage, st_ptr, payload, None, 0, stream)                    # NVLink read (kvx_copy)
                 evs[r][1].record(stream)
+                mine_t.copy_(peer_t)                                                        # same bytes, copy engines
+                evs[r][4].record(stream)
                 w.ctx.copy(tiny, tiny[32:], 16, w.remotes[0].flag_addr(2), r + 1, stream)   # P may reuse its image
                 evs[r][2].record(stream)
                 w.ctx.scatter(st_ptr, w.pool, d_dst[r % sets], n, xf, stream)
@@ -609,73 +683,193 @@ def run_pairs(args):
         torch.cuda.synchronize()
         dist.barrier()
         w.ctx.check()
+
+        # CPU-staged handoff of one request (set 0), twice, best: P gathers the raw blocks into its image (timed
+        # on P), D copies that image to pinned host memory (a D2H read of the PREFILL GPU's memory), transforms it
+        # with the C memcpy-per-row loop on all host threads, uploads and scatters
+        cpu_ms, g_raw_ms = None, None
         if is_p:
-            mine = {"gather_ms": min(e[0].elapsed_time(e[1]) for e in evs[1:])}
+            g_raw = []
+            for r in range(2):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                w.ctx.gather(w.pool, d_src[0], n, st_ptr, xf_raw, stream)
+                e1.record(stream)
+                w.ctx.copy(tiny, tiny[32:], 16, w.remotes[0].flag_addr(2), 100 + r, stream)
+                w.wait(2, 100 + r, 60000, stream)
+                torch.cuda.synchronize()
+                g_raw.append(e0.elapsed_time(e1))
+            g_raw_ms = min(g_raw)
+        else:
+            import ctypes
+
+            from oracle import kvx_oracle as o
+            from oracle import kvx_oracle_c as oc
+
+            words = shape.chunk_bytes() // 2
+            host_in = torch.empty(shape.regions, n, words, dtype=torch.int16).pin_memory()
+            host_out = torch.empty(shape.regions, n, words, dtype=torch.int16).pin_memory()
+            lib = oc.lib()
+            H, N, Dh = shape.kv_heads, shape.block_tokens, shape.head_dim
+            side = lambda t, layout: oc._Side(None, None, t.data_ptr(), 0, 0, layout, H, 0, 0)  # noqa: E731
+            t_cpu = []
+            for r in range(2):
+                w.wait(2, 100 + r, 60000, stream)
+                torch.cuda.synchronize()
+                t1 = time.perf_counter()
+                host_in.view(-1).copy_(peer_t.view(torch.int16), non_blocking=True)
+                torch.cuda.synchronize()
+                s_side, d_side = side(host_in, o.HND), side(host_out, o.NHD)
+                rc = lib.kvxo_xfer(ctypes.byref(s_side), ctypes.byref(d_side), shape.regions, n, N, H, Dh * 2, threads)
+                assert rc == 0
+                mine_t.view(torch.int16).copy_(host_out.view(-1), non_blocking=True)
+                w.ctx.scatter(st_ptr, w.pool, d_dst[0], n, xf, stream)
+                torch.cuda.synchronize()
+                t_cpu.append(time.perf_counter() - t1)
+                w.ctx.copy(tiny, tiny[32:], 16, w.remotes[0].flag_addr(2), 100 + r, stream)
+                torch.cuda.synchronize()
+            cpu_ms = 1e3 * min(t_cpu)
+            del host_in, host_out
+        dist.barrier()
+        if is_p:
+            mine = {"gather_ms": min(e[0].elapsed_time(e[1]) for e in evs[1:]), "gather_raw_ms": g_raw_ms}
         else:
             mine = {"copy_ms": min(e[0].elapsed_time(e[1]) for e in evs[1:]),
-                    "scatter_ms": min(e[2].elapsed_time(e[3]) for e in evs[1:])}
+                    "memcpy_ms": min(e[1].elapsed_time(e[4]) for e in evs[1:]),
+                    "scatter_ms": min(e[2].elapsed_time(e[3]) for e in evs[1:]), "cpu_staged_ms": cpu_ms}
             w.ctx.mem_unmap(peer_stage)
         allm = [None] * world
         dist.all_gather_object(allm, mine)
         if rank == 0:
             g = max(m["gather_ms"] for m in allm if "gather_ms" in m)
             c = max(m["copy_ms"] for m in allm if "copy_ms" in m)
+            mc = max(m["memcpy_ms"] for m in allm if "memcpy_ms" in m)
             sc = max(m["scatter_ms"] for m in allm if "scatter_ms" in m)
+            cs = max(m["cpu_staged_ms"] for m in allm if m.get("cpu_staged_ms")) + max(m["gather_raw_ms"] for m in allm if m.get("gather_raw_ms"))
             staged = {"gather_ms": round(g, 4), "gather_hbm_GBps": round(2 * payload / g / 1e6, 1),
                       "copy_ms": round(c, 4), "copy_nvlink_GBps": round(payload / c / 1e6, 1),
                       "copy_pct_of_nvlink_900": round(100 * payload / c / 1e6 / 900.0, 2),
                       "scatter_ms": round(sc, 4), "scatter_hbm_GBps": round(2 * payload / sc / 1e6, 1),
                       "note": "max over pairs of the best of 4 repetitions; copy = kvx_copy run by the decode GPU on the "
                               "prefill GPU's staging image"}
+            baselines = {"cudaMemcpyPeerAsync_GBps": round(payload / mc / 1e6, 1), "cudaMemcpyPeerAsync_ms": round(mc, 4),
+                         "cudaMemcpyPeerAsync_note": "the copy engines moving the same contiguous 1 GiB image between the same two GPUs "
+                                                     "(torch copy_ = cudaMemcpyAsync over UVA, the cudaMemcpyPeerAsync path), all pairs at once, max over pairs",
+                         "cpu_staged_GBps": round(payload / cs / 1e6, 2), "cpu_staged_ms": round(cs, 2), "cpu_staged_host_threads": threads,
+                         "cpu_staged_note": "one request: gather on the prefill GPU (timed there) + D2H of that image into pinned host memory, "
+                                            "memcpy-per-row HND->NHD on the host (oracle/kvx_oracle.c), H2D, scatter on the decode GPU; best of 2"}
         dist.barrier()
         w.ctx.mem_free(st_ptr)
 
-    # correctness of what landed (the last e2e step's set), checked by the decode rank on the device
-    ok = torch.ones(1, device="cuda")
+    # Bit-exactness of EVERYTHING that landed: the decode rank regenerates its prefill peer's pool from the seed
+    # (same generator, on this GPU — not through the mapping the transfer used), builds the expected decode pool
+    # for every block set the run touched, and compares the ENTIRE pool: touched blocks, canary blocks, block 0.
+    vstat = torch.zeros(3, dtype=torch.int64, device="cuda")  # [ok, touched blocks, canary blocks]
     if not is_p:
         canary = np.array(synth.CANARY16, dtype=np.uint16).view(np.int16).item()
         words = shape.chunk_bytes() // 2
-        v = w.kv.tensor().view(torch.int16).view(shape.regions, nb, words)
-        idx = torch.from_numpy(perm_d[: n * min(sets, total_steps)].astype(np.int64)).cuda()
-        if bool((v[:, idx[:n]] == canary).all()):
-            ok[0] = 0  # nothing arrived
-        if not bool((v[:, 0] == canary).all()):
-            ok[0] = 0  # null block written
+        dv = w.kv.tensor().view(torch.int16).view(shape.regions, nb, words)
+        src = harness.regen_random(torch, shape.regions * nb * words * 2, synth.SEED_BASE + 3000 + peer, local).view(shape.regions, nb, words)
+        exp = torch.full_like(dv, canary)
+        H, N, Dh = shape.kv_heads, shape.block_tokens, shape.head_dim
+        for s in sorted(used_sets):
+            si = torch.from_numpy(h_src[s].astype(np.int64)).cuda()
+            di = torch.from_numpy(h_dst[s].astype(np.int64)).cuda()
+            exp[:, di] = src[:, si].view(shape.regions, n, H, N, Dh).transpose(2, 3).reshape(shape.regions, n, words)
+        vstat[0] = int(torch.equal(exp, dv))
+        vstat[1] = len(used_sets) * n
+        vstat[2] = nb - len(used_sets) * n
+        del src, exp
+    ok = vstat[:1].clone() if not is_p else torch.ones(1, dtype=torch.int64, device="cuda")
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    dist.all_reduce(vstat[1:], op=dist.ReduceOp.SUM)
 
-    t = torch.tensor([ms, e2e_s * 1e3], device="cuda", dtype=torch.float64)
+    t = torch.tensor([ms, e2e_s * 1e3, ms_alone], device="cuda", dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     lt = torch.tensor([float(launches)], device="cuda", dtype=torch.float64)
     dist.all_reduce(lt, op=dist.ReduceOp.SUM)
-    ms_max, e2e_ms = float(t[0]), float(t[1])
+    ms_max, e2e_ms, alone_ms = float(t[0]), float(t[1]), float(t[2])
+    dist.barrier()
+    w.close()
+    torch.cuda.empty_cache()
+
+    # CPU baseline of the same request (host pools, the C restatement on every host thread), rank 0, bounded
+    cpu = None
+    if rank == 0 and not args.no_extras:
+        cpu_gbps, cpu_reps, _, _ = cpu_handoff_rate(shape, isl, min_seconds=6.0, max_reps=100, threads=threads)
+        cpu = {"value": round(cpu_gbps, 3), "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
+                         "oracle/kvx_oracle.c memcpy-per-row HND->NHD, the other ranks idle"}
+    dist.barrier()
+
+    # BASELINE.json configs #3, #4 and #5 as verified request streams (kvx.harness; not the headline)
+    legs = {}
+    if not args.no_extras:
+        M8, M70 = "meta-llama/Llama-3.1-8B", "meta-llama/Llama-3.1-70B"
+        topo = synthetic_topology(pairs, pairs, 1, 1, "vllm", M8, decode_layout=kvx.NHD)
+        for c in (1, 4):  # config #3's load shape: 64-request closed loop at ISL 8192 per pair, concurrency 1 and 4
+            cfg = harness.StreamConfig(model=M8, isl=[8192] * args.stream_requests, concurrency=c)
+            legs[f"config3_stream_isl8k_c{c}"] = brief(harness_leg(dist, rank, world, topo, cfg))
+        # config #5's: every pair its own stream of 32 requests, ISL log-uniform over 1k..32k, all pairs at once
+        choices = [1024, 2048, 4096, 8192, 16384, 32768]
+        per_rep = [harness.draw_isls(args.mixed_requests, choices, 5 + 17 * d) for d in range(pairs)]
+        cfg = harness.StreamConfig(model=M8, isl=per_rep[0], per_replica_isl=per_rep, concurrency=1)
+        legs["config5_mixed_isl"] = brief(harness_leg(dist, rank, world, topo, cfg))
+        # config #4's: TP reshard on transfer, prefill TP = 2 x decode TP, every edge concurrent.  6 of 8 GPUs run
+        # TP4 -> TP2 (Llama-3.1-70B); with 4 GPUs the same code runs TP2 -> TP1 on 3 of them.
+        if world >= 4:
+            ptp, dtp = (4, 2) if world >= 6 else (2, 1)
+            topo4 = synthetic_topology(1, 1, ptp, dtp, "vllm", M70)
+            cfg = harness.StreamConfig(model=M70, isl=[8192] * 8, concurrency=1)
+            s4 = harness_leg(dist, rank, world, topo4, cfg, group_ranks=list(range(ptp + dtp)))
+            legs[f"config4_tp{ptp}_to_tp{dtp}"] = brief(s4)
+
     if rank == 0:
         ms_step = ms_max / args.steps
         per_pair = payload / (ms_step / 1e3) / 1e9
+        alone = payload / (alone_ms / alone_steps / 1e3) / 1e9 if alone_ms > 0 else None
         value = pairs * per_pair
+        peak = baselines["cudaMemcpyPeerAsync_GBps"] if baselines else NVLINK_PEAK
+        traffic, traffic_src = pull_ncu_traffic() if (pull and isl == 8192) else (None, None)
+        verified = bool(ok[0] > 0)
         line = {
             "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8 (opaque bf16 bits)", "data": "synthetic",
             "config": workload_config(world, shape, isl),
+            "value_is": f"sum over the {pairs} concurrent P->D pair(s); one pair = per_pair_GBps",
             "per_pair_GBps": round(per_pair, 2), "pct_of_nvlink_900": round(100 * per_pair / 900.0, 2),
+            "one_pair_alone_GBps": round(alone, 2) if alone else None,
+            "pairs_efficiency_vs_one_pair_alone": round(per_pair / alone, 4) if alone else None,
             "e2e": {"value": round(pairs * args.steps * payload / (e2e_ms / 1e3) / 1e9, 2), "unit": UNIT,
                     "h2d_bytes_per_step": 8 * n, "d2h_bytes_per_step": 8, "ms_per_step": round(e2e_ms / args.steps, 4),
                     "through": f"{'DecodeWorker.pull' if pull else 'PrefillWorker.push'} -> kvx_handoff_host (host block-id "
                                "lists in, completion word back; release flag stored in the peer's memory)"},
             "gpu_launches": int(lt[0]), "clocks": clocks,
-            "roofline": {"bound": "nvlink", "achieved": round(per_pair, 1), "peak": NVLINK_PEAK, "unit": "GB/s",
-                         "frac": round(per_pair / NVLINK_PEAK, 4), "traffic": None,
-                         "peak_source": "measured peer copy 770 GB/s per direction (B200_PROFILING.md); nominal 900",
+            "roofline": {"bound": "nvlink", "achieved": round(per_pair, 1), "peak": peak, "unit": "GB/s",
+                         "frac": round(per_pair / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": ("measured in this run: the copy engines moving the same 1 GiB between the same two GPUs "
+                                         "(baselines.cudaMemcpyPeerAsync_GBps); nominal 900 per direction") if baselines else
+                                        "770 GB/s per direction (B200_PROFILING.md peer copy; --no-extras run); nominal 900",
                          "kernel": "kvx_xfer_tma_kernel (fused: " + ("peer gather over NVLink + transform + local scatter, run by the decode GPU)" if pull else "local gather + transform + peer store, run by the prefill GPU)"),
                          "algorithmic_bytes_per_launch": payload, "frac_of_nominal_900": round(per_pair / 900.0, 4)},
+            "cpu_baseline": cpu,
             "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-            "direction": args.mode, "landed_ok": bool(ok[0] > 0), "staged_path": staged,
+            "direction": args.mode,
+            "verified_bit_exact": verified, "blocks_checked": int(vstat[1]), "canary_blocks_checked": int(vstat[2]),
+            "verification": "every decode rank: ENTIRE pool (all regions of every block, block 0 included) against the expected pool "
+                            "rebuilt from the prefill rank's seed, after the timed, e2e, one-pair and staged runs",
+            "staged_path": staged, "baselines": baselines, **legs,
         }
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     os.close(json_fd)
+    bad = int(ok[0] <= 0)
+    leg_bad = [k for k, v in legs.items() if rank == 0 and v is not None and v.get("verified_bit_exact") is not True]
     dist.barrier()
-    w.close()
     dist.destroy_process_group()
+    if bad or leg_bad:
+        sys.stderr.write(f"bench: verification FAILED (headline {'bad' if bad else 'ok'}, legs {leg_bad})\n")
+        return 1
     return 0
 
 
@@ -687,6 +881,8 @@ def main():
     ap.add_argument("--impl", default="kvx", choices=["kvx", "reference"])
     ap.add_argument("--isl", type=int, default=8192)
     ap.add_argument("--no-extras", action="store_true", help="N=1: skip the per-kernel table, ISL sweep and CPU baseline (profiling runs)")
+    ap.add_argument("--stream-requests", type=int, default=64, help="N>1: requests per pair in the config #3 closed-loop streams")
+    ap.add_argument("--mixed-requests", type=int, default=32, help="N>1: requests per pair in the config #5 mixed-ISL stream")
     ap.add_argument("--mode", default="pull", choices=["pull", "push"],
                     help="N>1: decode GPU reads the prefill pool (pull, default) or prefill GPU stores into the decode pool")
     args = ap.parse_args()

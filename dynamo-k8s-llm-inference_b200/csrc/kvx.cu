@@ -1113,6 +1113,25 @@ int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len) try {
   return KVX_OK;
 } KVX_CATCH_ALL
 
+int32_t kvx_pool_region_base(const kvx_pool* pool, uint32_t region, void** base) try {
+  if (!pool || !base || region >= pool->base.size()) return KVX_EINVAL;
+  *base = pool->base[region];
+  return KVX_OK;
+} KVX_CATCH_ALL
+
+int32_t kvx_pool_slice(const kvx_pool* pool, uint32_t first_region, uint32_t count, kvx_pool** out) try {
+  if (!pool || !out || count == 0 || static_cast<uint64_t>(first_region) + count > pool->base.size()) return KVX_EINVAL;
+  kvx_pool_desc d = pool->desc;
+  d.regions = count;
+  d.base = pool->base.data() + first_region;
+  kvx_pool* view = nullptr;
+  int32_t rc = kvx_pool_register(pool->ctx, &d, &view);
+  if (rc) return rc;
+  view->local = pool->local;  // same memory as the parent, whoever mapped it
+  *out = view;
+  return KVX_OK;
+} KVX_CATCH_ALL
+
 int32_t kvx_pool_exportable(kvx_pool* pool, int32_t* across_processes) try {
   if (!pool || !across_processes) return KVX_EINVAL;
   *across_processes = 1;

@@ -83,6 +83,19 @@ class Pool:
         self.ctx._check(self.ctx.lib.kvx_pool_export(self.handle, buf, ctypes.byref(need)), "kvx_pool_export")
         return buf.raw[: need.value]
 
+    def region_base(self, region: int) -> int:
+        out = c_vp()
+        self.ctx._check(self.ctx.lib.kvx_pool_region_base(self.handle, region, ctypes.byref(out)), "kvx_pool_region_base")
+        return out.value
+
+    def slice(self, first_region: int, count: int) -> "Pool":
+        """The K/V regions of a group of layers as a pool of their own (kvx_pool_slice); release before `self`."""
+        h = c_vp()
+        self.ctx._check(self.ctx.lib.kvx_pool_slice(self.handle, first_region, count, ctypes.byref(h)), "kvx_pool_slice")
+        return Pool(self.ctx, h.value, regions=count, block_tokens=self.block_tokens, heads=self.heads,
+                    head_dim=self.head_dim, elem_bytes=self.elem_bytes, layout=self.layout, num_blocks=self.num_blocks,
+                    imported=self.imported)
+
     @property
     def exportable_across_processes(self) -> bool:
         out = c_i32()

@@ -6,6 +6,9 @@ Same required flags, same messages, same exit codes.  `-u` is either an OpenAI-c
 in the reference (driven by kvx/httpload.py with the shape of the reference's multi_convos_parallel.sh), or a
 transport URL:  kvx://local?manifest=<DynamoGraphDeployment yaml>[&isl=8192][&requests=64][&concurrency=1]
            kvx://local?prefill=4&decode=4[&ptp=4&dtp=2][&isl=1024,2048,...][&layout=nhd][&route=spread][&batch=8]
+           ...&arrival=bursty[&gap_ms=1.0][&burst=4]&route=sched   one bursty stream, booked by kvx/router.py
+           ...&layerwise=8&prefill_ms=20                            hand over in 8 layer groups behind a synthetic prefill
+Every request is verified bit for bit unless verify=0 is given; an unverified run says so and is never "verified".
 Results land under <output-dir>/<benchmark-name>/results.json; -p adds SVG plots from that tree.
 """
 from __future__ import annotations
@@ -91,11 +94,26 @@ def build_job(url: str, model: str):
     layout = {"nhd": 0, "hnd": 1}.get(q.get("layout", "").lower())
     requests = int(q.get("requests", 16))
     isls = [int(x) for x in q.get("isl", "8192").split(",")]
-    isl = [isls[0]] * requests if len(isls) == 1 else draw_isls(requests, isls, int(q.get("seed", 5)))
+    seed = int(q.get("seed", 5))
+    isl = [isls[0]] * requests if len(isls) == 1 else draw_isls(requests, isls, seed)
+    ready = None
+    if q.get("arrival"):
+        if q["arrival"] != "bursty":
+            raise ValueError(f"unknown arrival process '{q['arrival']}': expected bursty")
+        from .router import skewed_arrivals
+
+        ready = skewed_arrivals(requests, seed + 1, float(q.get("gap_ms", 1.0)), int(q.get("burst", 4)))
+    n_dec = sum(w.replicas for w in topo.role("decode"))
+    per_rep = None
+    if q.get("per_pair_seed") == "1" and len(isls) > 1 and ready is None:  # config #5: every pair draws its own stream
+        per_rep = [draw_isls(requests, isls, seed + 17 * d) for d in range(n_dec)]
+    corrupt = tuple(int(x) for x in q["corrupt"].split(",")) if q.get("corrupt") else None
     opts = {k: int(q[k]) for k in ("engine", "stages", "stage_bytes", "ctas_per_sm", "store_mode", "vec_bytes", "consumer_warps", "l2_hint", "pdl",
                                    "param_tables", "max_ctas") if k in q}
     cfg = StreamConfig(model=model, isl=isl, concurrency=int(q.get("concurrency", 1)), verify=q.get("verify", "1") != "0",
-                       decode_layout=layout, options=opts, route=q.get("route", "pair"), batch=int(q.get("batch", 1)))
+                       decode_layout=layout, options=opts, route=q.get("route", "pair"), batch=int(q.get("batch", 1)),
+                       ready_ms=ready, per_replica_isl=per_rep, layerwise=int(q.get("layerwise", 1)),
+                       prefill_ms=float(q.get("prefill_ms", 0.0)), corrupt=corrupt)
     return topo, cfg
 
 
@@ -137,7 +155,12 @@ def main(argv: Optional[List[str]] = None) -> int:
 
         for p in plot_dir(out_dir):
             print(f"plot: {p}")
-    return 0 if (summary.get("verified_bit_exact") in (True, None) and summary.get("prefill_blocks_released")) else 1
+    if summary.get("verified_bit_exact") is None:  # only ever the caller's own verify=0: say so, never call it verified
+        sys.stderr.write("warning: verify=0 — the bytes that landed were NOT checked\n")
+        return 0 if (not cfg.verify and summary.get("prefill_blocks_released")) else 1
+    ok = (summary["verified_bit_exact"] is True and summary.get("requests_verified") == summary.get("requests")
+          and summary.get("prefill_blocks_released"))
+    return 0 if ok else 1
 
 
 if __name__ == "__main__":

@@ -8,6 +8,16 @@ prefill worker's block ids (kv_transfer_params), pulls the blocks over NVLink wi
 / TP reshard in flight, and releases the prefill blocks.  Result names follow the metrics the
 reference's dashboard and images export (grafana-dynamo-dashboard-configmap.yaml:214 TTFT;
 vllm:nixl_xfer_time_seconds, nixl_bytes_transferred, nixl_num_descriptors).
+
+Every request is verified: when it has landed, its destination blocks are compared on the device with the
+expected transform of the source blocks (source contents regenerated from the prefill rank's seed on the decode
+GPU — not read back through the mapping that was just used — unless that does not fit in memory); at the end
+of the stream every block of the decode pool is checked once more: blocks a request still owns against their
+source, every other block against the canary.  A run without verification reports `verified_bit_exact: null`
+and the runner treats that as "not verified", never as success.
+
+`run_rank` is the per-process body; `run_stream` spawns the processes itself, `bench.py` calls `run_rank`
+from the ranks torchrun started.
 """
 from __future__ import annotations
 
@@ -17,7 +27,7 @@ import socket
 import statistics
 import time
 from dataclasses import asdict, dataclass, field
-from typing import Dict, List, Optional
+from typing import Dict, List, Optional, Tuple
 
 import numpy as np
 
@@ -32,15 +42,21 @@ RESIDENCY = 4  # a request's blocks are freed this many transfers later (stands 
 @dataclass
 class StreamConfig:
     model: str
-    isl: List[int]  # one entry per request of a pair's stream
+    isl: List[int]  # closed loop: one entry per request of EVERY decode replica's stream; with arrivals: one global list
     concurrency: int = 1
     verify: bool = True
     decode_layout: Optional[int] = None  # None = manifest's
     batch: int = 1  # > 1: the decode worker pulls this many queued requests per scheduler step in ONE launch
     #                  (kvx_handoff_batch; same-size TP only, route "pair")
     route: str = "pair"  # "pair": decode replica i reads prefill replica i % nP; "spread": request q of decode
-    #                       replica i reads prefill replica (i + q) % nP (with concurrency >= nP this is an incast)
+    #                       replica i reads prefill replica (i + q) % nP (with concurrency >= nP this is an incast);
+    #                       "sched": kvx/router.py books each request on the ingress/egress ports that are free first
     options: Dict[str, int] = field(default_factory=dict)  # kvx context options
+    per_replica_isl: Optional[List[List[int]]] = None  # closed loop: a list per decode replica (config #5: a seed per pair)
+    ready_ms: Optional[List[float]] = None  # arrival-driven: when each request's KV is ready (prefill done), from stream start
+    layerwise: int = 1        # > 1: hand each request over in this many layer groups, each as soon as it is "prefilled"
+    prefill_ms: float = 0.0   # layerwise: synthetic prefill time of one request on the prefill GPU (spread over its layers)
+    corrupt: Optional[Tuple[int, int]] = None  # test hook: flip one byte of request (decode replica, index) after it landed
 
 
 def draw_isls(requests: int, choices: List[int], seed: int) -> List[int]:
@@ -97,28 +113,206 @@ def _pre_allocate(num_blocks: int, counts: List[int], seed: int, hold: int) -> L
     return out
 
 
-def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamConfig, n_devices: int, out_dir: str):
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+# ----------------------------------------------------------------------------------------------------------
+# Request plan: who reads what from whom, identical on every rank (pure function of the configuration)
+# ----------------------------------------------------------------------------------------------------------
+@dataclass
+class Req:
+    d_rep: int
+    idx: int                 # position in decode replica d_rep's pull order
+    isl: int
+    n: int                   # blocks
+    p_rep: int
+    p_serial: int = 0        # position among the requests prefill replica p_rep serves (its allocation order)
+    ready_ms: Optional[float] = None  # None = closed loop (pull as soon as a slot frees)
+    q: int = 0               # global index (arrival-driven streams), else == idx
+
+
+def plan_requests(cfg: StreamConfig, shape: KVShape, n_p: int, n_d: int, payload_of) -> Dict[int, List[Req]]:
+    """Every decode replica's ordered list of requests.  `payload_of(n_blocks)` = bytes one request moves."""
+    from . import router
+
+    per_d: Dict[int, List[Req]] = {d: [] for d in range(n_d)}
+    if cfg.ready_ms is not None:
+        if len(cfg.ready_ms) != len(cfg.isl):
+            raise ValueError("ready_ms needs one entry per request")
+        counts = [shape.blocks_for(x) for x in cfg.isl]
+        plan = router.plan(cfg.route, cfg.ready_ms, [payload_of(n) for n in counts], n_p, n_d)
+        for a in sorted(plan, key=lambda a: (a.d, a.order)):
+            per_d[a.d].append(Req(a.d, a.order, cfg.isl[a.q], counts[a.q], a.p, ready_ms=a.ready_ms, q=a.q))
+    else:
+        if cfg.route == "sched":
+            raise ValueError("route=sched books requests by the time their KV is ready: give ready_ms (arrival=...)")
+        for d in range(n_d):
+            isls = cfg.per_replica_isl[d] if cfg.per_replica_isl else cfg.isl
+            for q, isl in enumerate(isls):
+                p = (d + q) % n_p if cfg.route == "spread" else d % n_p
+                per_d[d].append(Req(d, q, isl, shape.blocks_for(isl), p, q=q))
+    # serial number of each request on its prefill replica: order by (ready time, decode replica, index)
+    serial = [0] * n_p
+    for r in sorted((r for lst in per_d.values() for r in lst), key=lambda r: (r.ready_ms or 0.0, r.idx, r.d_rep)):
+        r.p_serial = serial[r.p_rep]
+        serial[r.p_rep] += 1
+    return per_d
+
+
+def _served_by(per_d: Dict[int, List[Req]], p_rep: int) -> List[Req]:
+    return sorted((r for lst in per_d.values() for r in lst if r.p_rep == p_rep), key=lambda r: r.p_serial)
+
+
+def _release_slot(p_serial: int, consumer: int, n_consumers: int, num_flags: int) -> int:
+    """Release flag in the prefill rank's memory: one per (request it serves, consuming decode TP rank), in the
+    lower half of its flags (the upper half announces layer groups)."""
+    return (p_serial * n_consumers + consumer) % (num_flags // 2)
+
+
+def regen_random(torch, nbytes: int, seed: int, device: int):
+    """The bytes synth.fill_random(pool, seed) wrote, regenerated on `device` (same generator, same chunking)."""
+    g = torch.Generator(device=f"cuda:{device}")
+    g.manual_seed(seed)
+    t = torch.empty(nbytes // 2, dtype=torch.int16, device=f"cuda:{device}")
+    step = 1 << 27  # int16 elements = 1 << 28 bytes, as in synth.fill_random
+    for off in range(0, t.numel(), step):
+        t[off:off + step].random_(-32768, 32768, generator=g)
+    return t
+
+
+class _Verifier:
+    """Device-side bit-exact checks of a decode rank, on a stream of its own so that they never sit between two
+    transfers of the stream being timed."""
+
+    REGION_STEP = 8  # regions compared per torch op (bounds the temporaries at ISL 32k to 0.5 GiB)
+
+    def __init__(self, torch, w, shape, nb, me, sources, p_tp, d_tp, hp, p_layouts):
+        self.torch, self.w, self.shape, self.nb, self.me = torch, w, shape, nb, me
+        self.p_tp, self.d_tp, self.hp = p_tp, d_tp, hp
+        self.stream = torch.cuda.Stream()
+        self.N, self.Dh = shape.block_tokens, shape.head_dim
+        self.hd = w.kv.heads
+        self.dv = w.kv.tensor().view(torch.int16).view(shape.regions, nb, self.N * self.hd * self.Dh)
+        self.src: Dict[int, object] = {}     # remote key → [regions, nb, words_p] int16 view of that prefill rank's pool
+        self.src_layout: Dict[int, int] = {}
+        self.mode: Dict[int, str] = {}
+        words_p = self.N * hp * self.Dh
+        need = shape.regions * nb * words_p * 2
+        for key, (p_rep, edge) in sources.items():
+            free, _ = torch.cuda.mem_get_info()
+            if need < 0.5 * free:
+                t = regen_random(torch, need, SEED + 1000 * p_rep + edge.p_rank, me.device)
+                self.mode[key] = "regenerated from the prefill rank's seed"
+            else:  # does not fit beside the pool: read the prefill rank's bytes through the peer mapping
+                from . import synth
+
+                t = synth.as_torch(w.remotes[key].pool.region_base(0), need, me.device).view(torch.int16)
+                self.mode[key] = "read through the peer mapping (regeneration would not fit)"
+            self.src[key] = t.view(shape.regions, nb, words_p)
+            self.src_layout[key] = p_layouts[key]
+        self.ok = torch.ones(1, dtype=torch.int32, device=f"cuda:{me.device}")
+        self.per_req: List[object] = []
+        self.canary = np.array(0xC0DE, dtype=np.uint16).view(np.int16).item()
+
+    def _canon(self, blocks, heads, layout):
+        """[regions', n, words] → [regions', n, N, heads, D] whatever the row order."""
+        from .api import NHD
+
+        r, n = blocks.shape[0], blocks.shape[1]
+        if layout == NHD:
+            return blocks.view(r, n, self.N, heads, self.Dh)
+        return blocks.view(r, n, heads, self.N, self.Dh).transpose(2, 3)
+
+    def _compare(self, remote: Dict[int, np.ndarray], local_ids: np.ndarray, edges: Dict[int, object], mask=None):
+        """Device scalar: do the destination blocks `local_ids` (optionally only those selected by the boolean
+        `mask`) hold the transform of the request's source blocks?"""
+        torch = self.torch
+        good = torch.ones((), dtype=torch.bool, device=self.ok.device)
+        if len(local_ids) == 0 or (mask is not None and not mask.any()):
+            return good
+        sel = np.nonzero(mask)[0] if mask is not None else np.arange(len(local_ids))
+        li = torch.from_numpy(local_ids[sel].astype(np.int64)).to(self.ok.device)
+        for key, edge in edges.items():
+            rid = remote[key]
+            tail = rid[len(rid) - len(local_ids):]  # prefix hit on the decode side: the LAST len(local) source blocks
+            ri = torch.from_numpy(tail[sel].astype(np.int64)).to(self.ok.device)
+            for r0 in range(0, self.shape.regions, self.REGION_STEP):
+                sl = slice(r0, min(self.shape.regions, r0 + self.REGION_STEP))
+                got = self._canon(self.dv[sl][:, li], self.hd, self.w.layout)
+                want = self._canon(self.src[key][sl][:, ri], self.hp, self.src_layout[key])
+                if self.p_tp != self.d_tp:
+                    want = want[:, :, :, edge.src_head_off:edge.src_head_off + edge.heads]
+                    got = got[:, :, :, edge.dst_head_off:edge.dst_head_off + edge.heads]
+                good = good & (got == want).all()
+        return good
+
+    def check_request(self, after, remote: Dict[int, np.ndarray], local_ids, edges, corrupt: bool = False):
+        """Queue the check of one landed request behind event `after`; returns the event that marks the check done."""
+        torch = self.torch
+        self.stream.wait_event(after)
+        with torch.cuda.stream(self.stream):
+            if corrupt and len(local_ids):
+                self.dv[self.shape.regions // 2, int(local_ids[len(local_ids) // 2]), 5] ^= 1
+            good = self._compare(remote, np.asarray(local_ids), edges)
+            self.per_req.append(good.to(torch.int32).reshape(1))
+            done = torch.cuda.Event()
+            done.record(self.stream)
+        return done
+
+    def finish(self, requests: List[Tuple[Dict[int, np.ndarray], np.ndarray, Dict[int, object]]]):
+        """End of stream: every block of the decode pool once more.  Walk the requests newest first; the blocks a
+        request still owns (no later request reused them) must hold its bytes, all blocks no request ever touched
+        must hold the canary (block 0 included)."""
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            owned = np.zeros(self.nb, dtype=bool)
+            final_ok = torch.ones((), dtype=torch.bool, device=self.ok.device)
+            blocks_final = 0
+            for remote, local_ids, edges in reversed(requests):
+                local_ids = np.asarray(local_ids)
+                mine = ~owned[local_ids]
+                if mine.any():
+                    final_ok = final_ok & self._compare(remote, local_ids, edges, mask=mine)
+                    blocks_final += int(mine.sum())
+                owned[local_ids] = True
+            untouched = torch.from_numpy(np.nonzero(~owned)[0].astype(np.int64)).to(self.ok.device)
+            canary_ok = torch.ones((), dtype=torch.bool, device=self.ok.device)
+            for r0 in range(0, self.shape.regions, self.REGION_STEP):
+                sl = slice(r0, min(self.shape.regions, r0 + self.REGION_STEP))
+                canary_ok = canary_ok & (self.dv[sl][:, untouched] == self.canary).all()
+            per = torch.cat(self.per_req) if self.per_req else torch.ones(0, dtype=torch.int32, device=self.ok.device)
+            self.stream.synchronize()
+            per_host = per.cpu().tolist()
+        return {"requests_verified": int(sum(per_host)), "requests_checked": len(per_host),
+                "first_bad_request": next((i for i, v in enumerate(per_host) if not v), None),
+                "final_blocks_checked": blocks_final, "final_blocks_ok": bool(final_ok),
+                "canary_blocks_checked": int(untouched.numel()), "canary_blocks_ok": bool(canary_ok),
+                "regions_per_block": self.shape.regions, "source_bytes": sorted(set(self.mode.values()))}
+
+
+def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) -> Optional[Dict]:
+    """One worker rank's part of the stream.  torch.distributed is initialised (any backend that moves Python
+    objects and barriers on CPU tensors), the rank's device is current.  Returns this rank's result record."""
     import torch
     import torch.distributed as dist
 
     from . import synth
-    from .api import HND, NHD
+    from .api import HND, NHD  # noqa: F401
     from .workers import DecodeWorker, PrefillWorker
 
-    plans = rank_plans(topo, n_devices)
+    world = len(plans)
     me = plans[rank]
-    torch.cuda.set_device(me.device)
-    dist.init_process_group("gloo", rank=rank, world_size=world)
     shape = KV_SHAPES[cfg.model]
     p_ranks = [p for p in plans if p.role == "prefill"]
     d_ranks = [p for p in plans if p.role == "decode"]
     p_tp, d_tp = p_ranks[0].tp_size, d_ranks[0].tp_size
     n_p_rep = 1 + max(p.replica for p in p_ranks)
-    counts = [shape.blocks_for(x) for x in cfg.isl]
-    nb = pool_blocks(shape, cfg.isl, cfg.concurrency)
-    hold = RESIDENCY + cfg.concurrency
+    n_d_rep = 1 + max(p.replica for p in d_ranks)
     edges = plan_edges(p_tp, d_tp, shape.kv_heads)
+    hp, hd = heads_per_rank(shape.kv_heads, p_tp), heads_per_rank(shape.kv_heads, d_tp)
+    chunk_d = shape.block_tokens * hd * shape.head_dim * shape.elem_bytes
+    per_d = plan_requests(cfg, shape, n_p_rep, n_d_rep, lambda n: n * shape.regions * chunk_d)
+    all_isl = [r.isl for lst in per_d.values() for r in lst] or [16]
+    c = max(1, cfg.concurrency)
+    nb = pool_blocks(shape, all_isl, c)
+    hold = RESIDENCY + c
     layout = me.layout if (me.role == "prefill" or cfg.decode_layout is None) else cfg.decode_layout
     Worker = PrefillWorker if me.role == "prefill" else DecodeWorker
     w = Worker(me.device, shape, nb, layout, tp_rank=me.tp_rank, tp_size=me.tp_size, seed=SEED + rank, **cfg.options)
@@ -128,193 +322,239 @@ def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamCo
         synth.fill_canary(w.kv)
     torch.cuda.synchronize()
     metas = [None] * world
-    dist.all_gather_object(metas, w.metadata())
-
-    # which prefill replica feeds request q of decode replica i
-    def src_replica(d_rep: int, q: int = 0) -> int:
-        return (d_rep + q) % n_p_rep if cfg.route == "spread" else d_rep % n_p_rep
+    dist.all_gather_object(metas, w.metadata(), group=group)
 
     def p_rank_of(rep: int, t: int) -> int:
         return next(p.rank for p in p_ranks if p.replica == rep and p.tp_rank == t)
 
-    result = None
-    if me.role == "prefill":
-        # block ids of every request of every stream this replica serves (same on all its TP ranks)
-        served = [d for d in d_ranks if d.tp_rank == 0 and
-                  any(src_replica(d.replica, q) == me.replica for q in range(len(counts)))]
-        ids = {d.replica: _pre_allocate(nb, counts, SEED + 7 + 100 * me.replica + d.replica, hold) for d in served}
-        box = [ids]
-    else:
-        box = [None]
-    all_ids = [None] * world
-    dist.all_gather_object(all_ids, box[0])
+    def d_rank_of(rep: int, t: int) -> int:
+        return next(p.rank for p in d_ranks if p.replica == rep and p.tp_rank == t)
 
+    # block ids: a pure function of the plan, so every rank computes the lists it needs itself
+    def prefill_ids(p_rep: int) -> List[np.ndarray]:
+        # prefill contents never change during a stream, so its ids only need to look like a live allocator's
+        return _pre_allocate(nb, [r.n for r in _served_by(per_d, p_rep)], SEED + 7 + 100 * p_rep, hold)
+
+    # consumers of prefill TP rank t: the decode TP ranks with an edge from it (fan-out when d_tp > p_tp)
+    def consumers_of(t: int) -> List[int]:
+        return sorted(e.d_rank for e in edges if e.p_rank == t)
+
+    G = max(1, cfg.layerwise)
+    result = None
     if me.role == "decode":
+        mine = per_d[me.replica]
         srcs = [e for e in edges if e.d_rank == me.tp_rank]
-        p_reps = sorted({src_replica(me.replica, q) for q in range(len(counts))})
+        p_reps = sorted({r.p_rep for r in mine})
+        sources, p_layouts = {}, {}
         for pr in p_reps:
             for e in srcs:
-                w.add_remote(pr * 1000 + e.p_rank, metas[p_rank_of(pr, e.p_rank)])
-        remote_ids = [all_ids[p_rank_of(src_replica(me.replica, q), 0)][me.replica][q] for q in range(len(counts))]
-        local_ids = _pre_allocate(nb, counts, SEED + 13 + 100 * me.replica, hold)  # same on all TP ranks of a replica
-        c = max(1, cfg.concurrency)
-        streams = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in cfg.isl]
-        chunk_local = shape.block_tokens * w.kv.heads * shape.head_dim * shape.elem_bytes
-        per_req, t_sub, t_done = [], [0.0] * len(counts), [0.0] * len(counts)
-        dist.barrier()
-        torch.cuda.synchronize()
-        t_begin = time.perf_counter()
-        batch = cfg.batch if (cfg.batch > 1 and len(srcs) == 1 and p_tp == d_tp and cfg.route == "pair") else 1
-        group_of = {}
-        if batch > 1:
-            # one scheduler step = up to `batch` queued requests, received in one launch; closed loop over steps
-            lane0 = streams[0][0]
-            key = src_replica(me.replica, 0) * 1000 + srcs[0].p_rank
-            for g0 in range(0, len(counts), batch):
-                qs = list(range(g0, min(len(counts), g0 + batch)))
-                t0 = time.perf_counter()
-                ev[g0][0].record(lane0)
-                w.pull_many(key, [(remote_ids[q], local_ids[q], (q * d_tp + me.tp_rank) % w.num_flags, q + 1, None) for q in qs],
-                            stream=lane0)
-                ev[g0][1].record(lane0)
-                ev[g0][1].synchronize()
-                t1 = time.perf_counter()
-                for q in qs:
-                    t_sub[q], t_done[q], group_of[q] = t0, t1, (g0, qs)
-        for q, n in enumerate(counts):
-            if batch > 1:
-                break
-            if q >= c:  # closed loop: at most c requests in flight
-                ev[q - c][1].synchronize()
-                t_done[q - c] = time.perf_counter()
-            lane = streams[q % c]
-            t_sub[q] = time.perf_counter()
-            ev[q][0].record(lane[0])
+                key = pr * 1000 + e.p_rank
+                w.add_remote(key, metas[p_rank_of(pr, e.p_rank)])
+                sources[key] = (pr, e)
+                p_layouts[key] = plans[p_rank_of(pr, e.p_rank)].layout
+        ids_of_p = {pr: prefill_ids(pr) for pr in p_reps}
+        remote_ids = [ids_of_p[r.p_rep][r.p_serial] for r in mine]
+        local_ids = _pre_allocate(nb, [r.n for r in mine], SEED + 13 + 100 * me.replica, hold)  # same on all TP ranks of a replica
+        ver = _Verifier(torch, w, shape, nb, me, sources, p_tp, d_tp, hp, p_layouts) if cfg.verify else None
+        lanes = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in mine]
+        ev_ready = [torch.cuda.Event(enable_timing=True) for _ in mine]  # gated streams: last layer group is ready
+        gated = G > 1 or cfg.prefill_ms > 0   # the pulls wait on the GPU for the prefill worker's "layers ready" flags
+        t_sub, t_done, t_ready = [0.0] * len(mine), [0.0] * len(mine), [0.0] * len(mine)
+        group_of: Dict[int, Tuple[int, List[int]]] = {}
+        checked_args: List[object] = [None] * len(mine)
+        # checks run on the verifier's stream in the order requests LAND; before request i reuses the blocks of
+        # requests <= i - hold - 1, every one of their checks must have read them: wait for the latest-queued of them
+        chk_events: List[object] = []
+        chk_pos: List[Optional[int]] = [None] * len(mine)
+        prefix = {"upto": -1, "pos": -1}
+
+        def wait_for_checks(i: int, streams) -> None:
+            limit = i - hold - 1
+            if ver is None or limit < 0:
+                return
+            while prefix["upto"] < limit:
+                prefix["upto"] += 1
+                prefix["pos"] = max(prefix["pos"], chk_pos[prefix["upto"]])
+            for s_ in streams:
+                s_.wait_event(chk_events[prefix["pos"]])
+
+        def remote_of(i: int) -> Dict[int, np.ndarray]:
+            return {mine[i].p_rep * 1000 + e.p_rank: remote_ids[i] for e in srcs}
+
+        def edges_of(i: int) -> Dict[int, object]:
+            return {mine[i].p_rep * 1000 + e.p_rank: e for e in srcs}
+
+        def flag_slot(i: int, e) -> int:
+            cons = consumers_of(e.p_rank)
+            return _release_slot(mine[i].p_serial, cons.index(me.tp_rank), len(cons), w.remotes[mine[i].p_rep * 1000 + e.p_rank].meta.num_flags)
+
+        def issue(i: int, lane) -> None:
+            """Queue request i on a lane: one pull per source edge (fan-in when p_tp > d_tp), joined on lane[0]."""
+            r = mine[i]
+            wait_for_checks(i, lane)
+            ev[i][0].record(lane[0])
             for j, e in enumerate(srcs):
                 if j:
-                    lane[j].wait_event(ev[q][0])
-                # release slot: one flag per (request, consumer TP rank) in the prefill rank's memory
-                w.pull(src_replica(me.replica, q) * 1000 + e.p_rank, remote_ids[q], local_ids[q], notify_slot=(q * d_tp + me.tp_rank) % w.num_flags,  # flag slot in the prefill rank's memory
-                       value=q + 1, edge=e if (p_tp != d_tp) else None, host_tables=True, stream=lane[j])
+                    lane[j].wait_event(ev[i][0])
+                key = r.p_rep * 1000 + e.p_rank
+                edge = e if (p_tp != d_tp) else None
+                if gated:
+                    for g in range(G):
+                        w.wait(w.layer_ready_slot(r.p_serial, g, G, w.num_flags, j, len(srcs)), r.p_serial + 1, 60000, lane[j])
+                        if g == G - 1 and j == 0:
+                            ev_ready[i].record(lane[0])
+                        w.pull_layers(key, remote_ids[i], local_ids[i], g, G,
+                                      notify_slot=flag_slot(i, e) if g == G - 1 else None, value=r.p_serial + 1,
+                                      edge=edge, stream=lane[j])
+                else:
+                    w.pull(key, remote_ids[i], local_ids[i], notify_slot=flag_slot(i, e), value=r.p_serial + 1,
+                           edge=edge, host_tables=True, stream=lane[j])
             for j in range(1, len(srcs)):
                 done_j = torch.cuda.Event()
                 done_j.record(lane[j])
                 lane[0].wait_event(done_j)
-            ev[q][1].record(lane[0])
-        for q in range(max(0, len(counts) - c), len(counts)):
-            if batch > 1:
-                break
-            ev[q][1].synchronize()
-            t_done[q] = time.perf_counter()
+            ev[i][1].record(lane[0])
+
+        def landed(i: int) -> None:
+            if ver is not None:
+                chk_events.append(ver.check_request(ev[i][1], remote_of(i), local_ids[i], edges_of(i),
+                                                    corrupt=cfg.corrupt is not None and tuple(cfg.corrupt) == (me.replica, i)))
+                chk_pos[i] = len(chk_events) - 1
+            checked_args[i] = (remote_of(i), local_ids[i], edges_of(i))
+
+        dist.barrier(group=group)
+        torch.cuda.synchronize()
+        t_begin = time.perf_counter()
+        now_ms = lambda: 1e3 * (time.perf_counter() - t_begin)  # noqa: E731
+        batch = cfg.batch if (cfg.batch > 1 and len(srcs) == 1 and p_tp == d_tp and cfg.route == "pair"
+                              and cfg.ready_ms is None and G == 1) else 1
+        if batch > 1:
+            # one scheduler step = up to `batch` queued requests, received in one launch; closed loop over steps
+            lane0 = lanes[0][0]
+            for g0 in range(0, len(mine), batch):
+                qs = list(range(g0, min(len(mine), g0 + batch)))
+                key = mine[g0].p_rep * 1000 + srcs[0].p_rank
+                wait_for_checks(g0, [lane0])
+                t0 = time.perf_counter()
+                ev[g0][0].record(lane0)
+                w.pull_many(key, [(remote_ids[i], local_ids[i], flag_slot(i, srcs[0]), mine[i].p_serial + 1, None) for i in qs],
+                            stream=lane0)
+                ev[g0][1].record(lane0)
+                ev[g0][1].synchronize()
+                t1 = time.perf_counter()
+                for i in qs:
+                    t_sub[i], t_done[i], group_of[i] = t0, t1, (g0, qs)
+                    ev[i] = ev[g0]
+                    landed(i)
+        else:
+            # at most c requests in flight, each on a lane of its own; a request becomes eligible when its KV is
+            # ready (arrival-driven) or at once (closed loop); FIFO in the planned order
+            nxt, inflight, free_lanes = 0, {}, list(range(c))
+            while nxt < len(mine) or inflight:
+                progressed = False
+                for i in list(inflight):
+                    if ev[i][1].query():
+                        t_done[i] = time.perf_counter()
+                        free_lanes.append(inflight.pop(i))
+                        landed(i)
+                        progressed = True
+                while nxt < len(mine) and free_lanes and (mine[nxt].ready_ms is None or mine[nxt].ready_ms <= now_ms()):
+                    lane_id = free_lanes.pop(0)
+                    t_sub[nxt] = time.perf_counter()
+                    t_ready[nxt] = t_begin + (mine[nxt].ready_ms or 0.0) / 1e3 if mine[nxt].ready_ms is not None else t_sub[nxt]
+                    issue(nxt, lanes[lane_id])
+                    inflight[nxt] = lane_id
+                    nxt += 1
+                    progressed = True
+                if not progressed and not inflight and nxt < len(mine):
+                    wait = mine[nxt].ready_ms - now_ms()
+                    if wait > 0.2:
+                        time.sleep((wait - 0.1) / 1e3)
         torch.cuda.synchronize()
         t_end = time.perf_counter()
         w.ctx.check()
-        for q, n in enumerate(counts):
-            b = n * shape.regions * chunk_local
-            if q in group_of:  # batched: the step's requests complete together; rate = the step's bytes over its time
-                g0, qs = group_of[q]
+        per_req = []
+        for i, r in enumerate(mine):
+            b = r.n * shape.regions * chunk_d
+            if i in group_of:  # batched: the step's requests complete together; rate = the step's bytes over its time
+                g0, qs = group_of[i]
                 xfer = ev[g0][0].elapsed_time(ev[g0][1]) / 1e3
-                rate = sum(counts[x] for x in qs) * shape.regions * chunk_local / xfer / 1e9
+                rate = sum(mine[x].n for x in qs) * shape.regions * chunk_d / xfer / 1e9
+                ttft = 1e3 * (t_done[i] - t_sub[i])
             else:
-                xfer = ev[q][0].elapsed_time(ev[q][1]) / 1e3
-                rate = b / xfer / 1e9
-            per_req.append({"request": q, "isl": cfg.isl[q], "num_blocks": n, "bytes_transferred": b,
-                            "num_descriptors": n * shape.regions * len(srcs), "xfer_time_seconds": xfer,
-                            "throughput_GBps": rate, "batched_with": len(group_of[q][1]) if q in group_of else 1,
-                            "time_to_first_token_added_ms": 1e3 * (t_done[q] - t_sub[q])})
-        ok = True
-        if cfg.verify:
-            ok = _verify_tail(torch, w, shape, srcs, p_tp, d_tp, src_replica(me.replica, len(counts) - 1), remote_ids, local_ids, counts, nb,
-                              me, HND, NHD)
+                xfer = ev[i][0].elapsed_time(ev[i][1]) / 1e3
+                rate = b / xfer / 1e9 if xfer > 0 else 0.0
+                ttft = 1e3 * (t_done[i] - t_ready[i])
+            after_prefill = ev_ready[i].elapsed_time(ev[i][1]) if (gated and i not in group_of) else None
+            per_req.append({"request": r.q, "added_after_prefill_ms": after_prefill, "isl": r.isl, "num_blocks": r.n, "bytes_transferred": b, "prefill_replica": r.p_rep,
+                            "num_descriptors": r.n * shape.regions * len(srcs), "xfer_time_seconds": xfer,
+                            "throughput_GBps": rate, "batched_with": len(group_of[i][1]) if i in group_of else 1,
+                            "ready_ms": r.ready_ms, "queued_ms": 1e3 * (t_sub[i] - t_ready[i]) if i not in group_of else 0.0,
+                            "time_to_first_token_added_ms": ttft})
+        verdict = ver.finish([a_ for a_ in checked_args if a_ is not None]) if ver is not None else None
+        ok = None
+        if verdict is not None:
+            ok = (verdict["requests_verified"] == len(mine) and verdict["final_blocks_ok"] and verdict["canary_blocks_ok"])
         total_b = sum(r["bytes_transferred"] for r in per_req)
         result = {"rank": rank, "role": "decode", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
                   "sources": [e.p_rank for e in srcs], "wall_seconds": t_end - t_begin, "bytes_transferred": total_b,
-                  "ingress_GBps": total_b / (t_end - t_begin) / 1e9, "verified": bool(ok), "requests": per_req}
+                  "ingress_GBps": total_b / (t_end - t_begin) / 1e9, "verified": ok, "verification": verdict,
+                  "requests": per_req}
     else:
-        dist.barrier()
+        served = _served_by(per_d, me.replica)
+        cons = consumers_of(me.tp_rank)
+        # which decode ranks read this prefill rank: handshake with them when the stream is layer-wise (the
+        # "layers ready" flags live in THEIR memory)
+        gated = G > 1 or cfg.prefill_ms > 0
+        if gated:
+            for r_ in {(r.d_rep, t) for r in served for t in cons}:
+                w.add_remote(r_[0] * 1000 + r_[1], metas[d_rank_of(*r_)])
+        from .control import LeaseTable
+
+        leases = LeaseTable(lease_seconds=600.0)
+        for r in served:
+            if cons:
+                leases.grant(f"{r.p_serial}", consumers=len(cons))
+        dist.barrier(group=group)
+        t_begin = time.perf_counter()
+        if gated:
+            # synthetic prefill: each request's layers become ready group by group, prefill_ms per request, one
+            # request after the other on the prefill GPU (a device-side spin stands in for the layer kernels)
+            stream = torch.cuda.current_stream()
+            per_group_cycles = int(cfg.prefill_ms / G * 1e-3 * 1.9e9)  # ~SM clock; only the order of magnitude matters
+            for r in served:
+                for g in range(G):
+                    if per_group_cycles > 0:
+                        torch.cuda._sleep(per_group_cycles)
+                    for t in cons:  # my position among the prefill ranks decode rank t reads (fan-in when p_tp > d_tp)
+                        feeders = sorted(e.p_rank for e in edges if e.d_rank == t)
+                        w.publish_layers(r.d_rep * 1000 + t, r.p_serial, g, G, stream, src=feeders.index(me.tp_rank),
+                                         n_src=len(feeders))
         # the producer side only learns of completion through release flags written by the consumers
-        consumers = d_tp // p_tp if d_tp > p_tp else 1
-        deadline = time.time() + 120
-        pending = set()
-        for dr in sorted(ids):  # the last request of every stream that routes to this replica
-            mine = [q for q in range(len(counts)) if src_replica(dr, q) == me.replica]
-            if mine:
-                for t in range(d_tp):
-                    if any(e.p_rank == me.tp_rank and e.d_rank == t for e in edges):
-                        pending.add((mine[-1], t))
+        deadline = time.time() + 600
+        pending = {(r.p_serial, ci) for r in served for ci in range(len(cons))}
+        released = 0
         while pending and time.time() < deadline:
-            for key in list(pending):
-                q_last, t = key
-                if w.poll((q_last * d_tp + t) % w.num_flags, q_last + 1):
+            for key in sorted(pending)[:64]:
+                serial, ci = key
+                if w.poll(_release_slot(serial, ci, len(cons), w.num_flags), serial + 1):
                     pending.discard(key)
-            time.sleep(0.002)
+                    if leases.release(f"{serial}"):
+                        released += 1
+            time.sleep(0.001)
         result = {"rank": rank, "role": "prefill", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
-                  "released": not pending, "consumers_per_request": consumers}
+                  "released": not pending and len(leases) == 0, "requests_served": len(served), "requests_released": released,
+                  "consumers_per_request": len(cons)}
     gathered = [None] * world
-    dist.all_gather_object(gathered, result)
-    dist.barrier()
+    dist.all_gather_object(gathered, result, group=group)
+    dist.barrier(group=group)
     w.close()
-    if rank == 0:
-        with open(os.path.join(out_dir, "ranks.json"), "w") as f:
-            json.dump(gathered, f)
-    dist.destroy_process_group()
+    result["all"] = gathered if rank == plans[0].rank else None
+    return result
 
 
-def _verify_tail(torch, w, shape, srcs, p_tp, d_tp, p_rep, remote_ids, local_ids, counts, nb, me, HND, NHD) -> bool:
-    """Regenerate each source prefill rank's pool contents on this GPU (same seed, same generator) and
-    compare the last request's destination blocks with the expected transform, with torch ops only."""
-    q = len(counts) - 1
-    n = counts[q]
-    N, Dh = shape.block_tokens, shape.head_dim
-    hd = w.kv.heads
-    words_d = N * hd * Dh
-    dv = w.kv.tensor().view(torch.int16).view(shape.regions, nb, words_d)
-    li = torch.from_numpy(local_ids[q].astype(np.int64)).cuda()
-    got = dv[:, li]
-    got = got.view(shape.regions, n, N, hd, Dh) if w.layout == NHD else got.view(shape.regions, n, hd, N, Dh).transpose(2, 3)
-    ok = True
-    hp = heads_per_rank(shape.kv_heads, p_tp)
-    for e in srcs:
-        g = torch.Generator(device=f"cuda:{me.device}")
-        g.manual_seed(SEED + 1000 * p_rep + e.p_rank)
-        words_p = N * hp * Dh
-        src = torch.empty(shape.regions * nb * words_p, dtype=torch.int16, device="cuda")
-        step = 1 << 27
-        for off in range(0, src.numel(), step):  # same chunking as synth.fill_random (1<<28 bytes)
-            src[off:off + step].random_(-32768, 32768, generator=g)
-        sv = src.view(shape.regions, nb, words_p)
-        ri = torch.from_numpy(remote_ids[q][len(remote_ids[q]) - n:].astype(np.int64)).cuda()
-        blk = sv[:, ri].view(shape.regions, n, hp, N, Dh).transpose(2, 3)  # prefill pools are HND here → [.., N, hp, D]
-        if p_tp != d_tp:
-            want = blk[:, :, :, e.src_head_off:e.src_head_off + e.heads]
-            have = got[:, :, :, e.dst_head_off:e.dst_head_off + e.heads]
-        else:
-            want, have = blk, got
-        ok = ok and bool(torch.equal(want, have))
-        del src
-    return ok
-
-
-def run_stream(topo: Topology, cfg: StreamConfig, out_dir: str, n_devices: Optional[int] = None) -> Dict:
-    """Spawn one process per worker rank, run the stream, collect per-request records and a summary."""
-    import torch
-    import torch.multiprocessing as mp
-
-    if not torch.cuda.is_available():
-        raise RuntimeError("the kvx harness needs CUDA devices: there is no CPU fallback")
-    if not topo.disaggregated:
-        raise ValueError("the manifest has no prefill/decode split: nothing is handed off in aggregated mode")
-    if any(w.layout != 1 for w in topo.role("prefill")) and cfg.verify:
-        cfg.verify = False  # the torch cross-check assumes HND prefill pools
-    n_devices = n_devices or torch.cuda.device_count()
-    plans = rank_plans(topo, n_devices)
-    world = len(plans)
-    os.makedirs(out_dir, exist_ok=True)
-    port = _free_port()
-    mp.spawn(_worker_main, args=(world, port, topo, cfg, n_devices, out_dir), nprocs=world, join=True)
-    with open(os.path.join(out_dir, "ranks.json")) as f:
-        ranks = json.load(f)
+def summarize(ranks: List[Dict], topo_desc: Dict, cfg: StreamConfig, world: int, n_devices: int) -> Dict:
     dec = [r for r in ranks if r and r["role"] == "decode"]
     pre = [r for r in ranks if r and r["role"] == "prefill"]
     reqs = [q for r in dec for q in r["requests"]]
@@ -327,8 +567,16 @@ def run_stream(topo: Topology, cfg: StreamConfig, out_dir: str, n_devices: Optio
     wall = max(r["wall_seconds"] for r in dec)
     total = sum(r["bytes_transferred"] for r in dec)
     shape = KV_SHAPES[cfg.model]
+    by_isl: Dict[int, List[Dict]] = {}
+    for q in reqs:
+        by_isl.setdefault(q["isl"], []).append(q)
+    verified = None
+    if cfg.verify:
+        verified = all(r["verified"] is True for r in dec)
+    ver = [r["verification"] for r in dec if r.get("verification")]
     summary = {
-        "topology": topo.describe(), "model": asdict(shape), "isl": cfg.isl, "concurrency": cfg.concurrency,
+        "topology": topo_desc, "model": asdict(shape), "isl": sorted(by_isl), "concurrency": cfg.concurrency,
+        "route": cfg.route, "layerwise": cfg.layerwise, "arrival_driven": cfg.ready_ms is not None,
         "gpus_visible": n_devices, "ranks": world, "oversubscribed": world > n_devices,
         "requests": len(reqs), "bytes_transferred": total, "wall_seconds": wall,
         "aggregate_throughput_GBps": total / wall / 1e9,
@@ -336,13 +584,61 @@ def run_stream(topo: Topology, cfg: StreamConfig, out_dir: str, n_devices: Optio
         "per_edge_throughput_GBps_median": statistics.median(q["throughput_GBps"] for q in reqs) / max(1, len(dec[0]["sources"])),
         "per_request_throughput_GBps_median": statistics.median(q["throughput_GBps"] for q in reqs),
         "pct_of_nvlink_900": 100 * statistics.median(q["throughput_GBps"] for q in reqs) / 900.0,
+        "per_isl": {str(k): {"requests": len(v), "throughput_GBps_median": statistics.median(q["throughput_GBps"] for q in v),
+                             "time_to_first_token_added_ms_p50": pct(sorted(q["time_to_first_token_added_ms"] for q in v), 0.5),
+                             "time_to_first_token_added_ms_p90": pct(sorted(q["time_to_first_token_added_ms"] for q in v), 0.9)}
+                    for k, v in sorted(by_isl.items())},
         "xfer_time_seconds": {"p50": pct(xfer, 0.5), "p90": pct(xfer, 0.9), "max": xfer[-1]},
-        "time_to_first_token_added_ms": {"p50": pct(ttft, 0.5), "p90": pct(ttft, 0.9), "max": ttft[-1]},
+        "time_to_first_token_added_ms": {"p50": pct(ttft, 0.5), "p90": pct(ttft, 0.9), "max": ttft[-1],
+                                         "mean": sum(ttft) / len(ttft)},
         "num_descriptors": sum(q["num_descriptors"] for q in reqs),
-        "verified_bit_exact": all(r["verified"] for r in dec) if cfg.verify else None,
+        "verified_bit_exact": verified, "verification": "every request when it lands + the whole decode pool at the end" if cfg.verify else "off (verify=0)",
+        "requests_verified": sum(v["requests_verified"] for v in ver) if ver else 0,
+        "blocks_checked": sum(v["final_blocks_checked"] for v in ver) if ver else 0,
+        "canary_blocks_checked": sum(v["canary_blocks_checked"] for v in ver) if ver else 0,
+        "verification_source_bytes": sorted({s for v in ver for s in v["source_bytes"]}),
         "prefill_blocks_released": all(r["released"] for r in pre),
+        "releases_observed": sum(r["requests_released"] for r in pre), "releases_expected": sum(r["requests_served"] for r in pre if r["consumers_per_request"]),
         "seed": SEED,
     }
+    return summary
+
+
+def _worker_main(rank: int, world: int, port: int, topo: Topology, cfg: StreamConfig, n_devices: int, out_dir: str):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    import torch
+    import torch.distributed as dist
+
+    plans = rank_plans(topo, n_devices)
+    torch.cuda.set_device(plans[rank].device)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    result = run_rank(rank, plans, cfg)
+    if rank == 0:
+        with open(os.path.join(out_dir, "ranks.json"), "w") as f:
+            json.dump(result["all"], f)
+    dist.destroy_process_group()
+
+
+def run_stream(topo: Topology, cfg: StreamConfig, out_dir: str, n_devices: Optional[int] = None) -> Dict:
+    """Spawn one process per worker rank, run the stream, collect per-request records and a summary."""
+    import torch
+    import torch.multiprocessing as mp
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("the kvx harness needs CUDA devices: there is no CPU fallback")
+    if not topo.disaggregated:
+        raise ValueError("the manifest has no prefill/decode split: nothing is handed off in aggregated mode")
+    n_devices = n_devices or torch.cuda.device_count()
+    plans = rank_plans(topo, n_devices)
+    world = len(plans)
+    os.makedirs(out_dir, exist_ok=True)
+    port = _free_port()
+    mp.spawn(_worker_main, args=(world, port, topo, cfg, n_devices, out_dir), nprocs=world, join=True)
+    with open(os.path.join(out_dir, "ranks.json")) as f:
+        ranks = json.load(f)
+    summary = summarize(ranks, topo.describe(), cfg, world, n_devices)
+    dec = [r for r in ranks if r and r["role"] == "decode"]
+    pre = [r for r in ranks if r and r["role"] == "prefill"]
     with open(os.path.join(out_dir, "results.json"), "w") as f:
         json.dump({"summary": summary, "decode_ranks": dec, "prefill_ranks": pre}, f, indent=1)
     return summary

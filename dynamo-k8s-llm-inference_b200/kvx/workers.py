@@ -127,6 +127,28 @@ class _Worker:
     def poll(self, slot: int, value: int) -> bool:
         return self.ctx.flag_poll(self.flag_addr(slot), value)
 
+    # -- layer groups (layer-wise handoff) -------------------------------------------------------------
+    def layer_groups(self, groups: int):
+        """Region ranges (first, count) of `groups` contiguous groups of layers; a layer is its K and V region."""
+        layers = self.shape.layers
+        if not 1 <= groups <= layers:
+            raise ValueError(f"{groups} layer groups for {layers} layers")
+        cuts = [round(g * layers / groups) for g in range(groups + 1)]
+        return [(2 * cuts[g], 2 * (cuts[g + 1] - cuts[g])) for g in range(groups)]
+
+    def _slices(self, pool: Pool, tag, groups: int):
+        cache = self.__dict__.setdefault("_slice_cache", {})
+        if (tag, groups) not in cache:
+            cache[(tag, groups)] = [pool.slice(first, count) for first, count in self.layer_groups(groups)]
+        return cache[(tag, groups)]
+
+    @staticmethod
+    def layer_ready_slot(seq: int, group: int, groups: int, num_flags: int, src: int = 0, n_src: int = 1) -> int:
+        """Flag slot (upper half of the receiver's flags) that says "layer group `group` of request `seq` is ready"
+        on the `src`-th of the `n_src` prefill TP ranks this decode rank reads (fan-in when prefill TP > decode TP)."""
+        half = num_flags // 2
+        return half + ((seq * groups + group) * n_src + src) % half
+
     def _move(self, src_pool, src_ids, dst_pool, dst_ids, n, xf, flag, value, host_tables, h_done, stream):
         if host_tables:
             self.ctx.handoff_host(src_pool, np.ascontiguousarray(src_ids, dtype=np.int32), dst_pool,
@@ -135,6 +157,9 @@ class _Worker:
             self.ctx.handoff_fused(src_pool, src_ids, dst_pool, dst_ids, n, xf, flag, value, stream)
 
     def close(self) -> None:
+        for views in self.__dict__.get("_slice_cache", {}).values():
+            for v in views:
+                v.release()
         for r in self.remotes.values():
             r.pool.release()
         self.kv.free()
@@ -171,6 +196,24 @@ class DecodeWorker(_Worker):
         self._move(rem.pool, remote_ids, self.pool, local_ids, len(local_ids), xf, flag, value, host_tables, h_done, stream)
 
 
+    def pull_layers(self, key: int, remote_ids, local_ids, group: int, groups: int, *, seq: Optional[int] = None,
+                    notify_slot: Optional[int] = None, value: int = 1, edge: Optional[TPEdge] = None, h_done=None,
+                    timeout_ms: int = 10000, src: int = 0, n_src: int = 1, stream=None) -> None:
+        """Layer-wise handoff, receiving side: pull ONE group of layers of a request as soon as the prefill worker
+        has produced it, so that the transfer overlaps the rest of prefill (the router-level behaviour SURVEY.md
+        §8f.4 names; the reference's manifests leave it to the images).  With `seq` the pull first waits, ON THE
+        STREAM, for PrefillWorker.publish_layers(seq, group) — no host round trip between "layers ready" and the
+        pull.  The release flag (`notify_slot`) is normally given with the last group only."""
+        rem = self.remotes[key]
+        xf = edge.xform(self.layout) if edge else None
+        src = self._slices(rem.pool, key, groups)[group]
+        dst = self._slices(self.pool, "own", groups)[group]
+        if seq is not None:
+            self.wait(self.layer_ready_slot(seq, group, groups, self.num_flags, src, n_src), seq + 1, timeout_ms, stream)
+        flag = rem.flag_addr(notify_slot) if notify_slot is not None else None
+        r, l = align_tables(np.asarray(remote_ids, np.int32), np.asarray(local_ids, np.int32))
+        self._move(src, r, dst, l, len(l), xf, flag, value, True, h_done, stream)
+
     def pull_many(self, key: int, requests, *, edge: Optional[TPEdge] = None, stream=None) -> None:
         """All the requests a scheduler step has to receive from one prefill worker, in one launch
         (= the loop over reqs_to_recv in vllm v1/nixl/worker.py:1933-1968).  `requests` is a sequence of
@@ -191,6 +234,14 @@ class PrefillWorker(_Worker):
     the same fused kernel (prefill GPU gathers and stores into the decode worker's slots)."""
 
     role = "prefill"
+
+    def publish_layers(self, key: int, seq: int, group: int, groups: int, stream=None, *, src: int = 0, n_src: int = 1) -> None:
+        """Layer-wise handoff, producing side: everything queued on `stream` so far has written layer group
+        `group` of request `seq` — tell decode worker `key` (an 8-byte store into ITS flag memory, ordered on the
+        stream behind the prefill kernels), which lets its pull_layers(…, seq=seq) go."""
+        rem = self.remotes[key]
+        slot = self.layer_ready_slot(seq, group, groups, rem.meta.num_flags, src, n_src)
+        self.ctx.flag_reset(rem.flag_addr(slot), seq + 1, stream)
 
     def push(self, key: int, src_ids, dst_ids, *, slot: int, value: int, edge: Optional[TPEdge] = None,
              host_tables: bool = True, h_done=None, stream=None) -> None:

@@ -154,6 +154,13 @@ int32_t kvx_pool_chunk_bytes(const kvx_pool* pool, uint64_t* bytes);
 /* = agent metadata + add_remote_agent: descriptor + peer handles of every region. */
 int32_t kvx_pool_export(kvx_pool* pool, void* buf, size_t* len);
 int32_t kvx_pool_import(kvx_ctx* ctx, const void* buf, size_t len, kvx_pool** out);
+/* Device address of one region (as registered, or as mapped by kvx_pool_import). */
+int32_t kvx_pool_region_base(const kvx_pool* pool, uint32_t region, void** base);
+/* A pool made of `count` consecutive regions of another (registered or imported) pool: the K and V of a group
+ * of layers.  Layer-wise handoff — sending a layer group as soon as prefill has produced it, so that the
+ * transfer overlaps the tail of prefill — is a handoff between two such slices; the block tables are the
+ * request's own.  The slice maps nothing and owns nothing but its record: release it before its parent. */
+int32_t kvx_pool_slice(const kvx_pool* pool, uint32_t first_region, uint32_t count, kvx_pool** out);
 /* Can another PROCESS import this pool?  *across_processes = 1 when every region lies in a plain
  * cudaMalloc allocation (CUDA IPC handle available), 0 for memory without one (VMM / expandable
  * segments, stream-ordered pools): such a pool still exports to contexts of the same process, and

@@ -58,8 +58,9 @@ def main():
     from kvx import synth
     from kvx.workers import DecodeWorker, PrefillWorker
 
-    dev = rank % torch.cuda.device_count()
+    dev = rank % torch.cuda.device_count()   # two devices when the box has them: then every byte crosses NVLink
     torch.cuda.set_device(dev)
+    print(f"rank {rank} uses cuda:{dev} of {torch.cuda.device_count()} visible ({torch.cuda.get_device_properties(dev).uuid})", flush=True)
     src_host = o.make_pool(shape.layers, 8, 64, nb_p, o.HND, seed=77)
     if rank == 0:
         w = PrefillWorker(dev, shape, nb_p, kvx.HND)

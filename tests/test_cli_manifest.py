@@ -168,3 +168,84 @@ def test_runner_tp_reshard_on_gpu(tmp_path):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
     s = json.load(open(out / "tp" / "results.json"))["summary"]
     assert s["verified_bit_exact"] is True and s["ranks"] == 6
+
+
+def test_build_job_stream_options():
+    from kvx.cli import build_job
+
+    _, cfg = build_job("kvx://local?prefill=4&decode=4&isl=1024,32768&requests=12&arrival=bursty&gap_ms=0.5&route=sched",
+                       "meta-llama/Llama-3.1-8B")
+    assert cfg.route == "sched" and len(cfg.ready_ms) == 12 and cfg.ready_ms == sorted(cfg.ready_ms)
+    _, cfg = build_job("kvx://local?prefill=2&decode=2&isl=1024,2048&requests=5&per_pair_seed=1", "meta-llama/Llama-3.1-8B")
+    assert len(cfg.per_replica_isl) == 2 and cfg.per_replica_isl[0] != cfg.per_replica_isl[1]
+    _, cfg = build_job("kvx://local?isl=8192&requests=2&layerwise=8&prefill_ms=20&corrupt=0,1", "meta-llama/Llama-3.1-8B")
+    assert cfg.layerwise == 8 and cfg.prefill_ms == 20.0 and cfg.corrupt == (0, 1)
+    with pytest.raises(ValueError):
+        build_job("kvx://local?arrival=poisson", "meta-llama/Llama-3.1-8B")
+
+
+M1B = "meta-llama/Llama-3.2-1B-Instruct"
+
+
+@pytest.mark.gpu
+def test_runner_verifies_every_request_and_fails_on_one_bad_byte(tmp_path):
+    """Every request of every decode rank is compared bit for bit when it lands, and the whole decode pool at the
+    end; one flipped byte in one landed block of one request turns the run into exit code 1."""
+    out = tmp_path / "r"
+    url = "kvx://local?prefill=1&decode=1&isl=256,1024&requests=12&concurrency=2"
+    r = _run("-u", url, "-m", M1B, "-o", str(out), "-b", "good")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    s = json.load(open(out / "good" / "results.json"))["summary"]
+    assert s["verified_bit_exact"] is True and s["requests_verified"] == s["requests"] == 12
+    assert s["canary_blocks_checked"] > 0 and s["blocks_checked"] > 0 and s["releases_observed"] == s["releases_expected"] == 12
+    r = _run("-u", url + "&corrupt=0,7", "-m", M1B, "-o", str(out), "-b", "bad")
+    assert r.returncode == 1, r.stdout[-2000:]
+    s = json.load(open(out / "bad" / "results.json"))["summary"]
+    assert s["verified_bit_exact"] is False and s["requests_verified"] == 11
+    # verification switched off by the caller: reported as not verified, with a warning, never as verified
+    r = _run("-u", url + "&verify=0", "-m", M1B, "-o", str(out), "-b", "off")
+    assert r.returncode == 0 and "NOT checked" in r.stderr
+    s = json.load(open(out / "off" / "results.json"))["summary"]
+    assert s["verified_bit_exact"] is None and s["verification"].startswith("off")
+
+
+@pytest.mark.gpu
+def test_runner_nhd_prefill_pools_are_verified_too(tmp_path):
+    """SGLang-style token-major prefill pools (backend=sglang → NHD on both sides) and NHD prefill → HND decode."""
+    out = tmp_path / "r"
+    for name, extra in (("nhd_nhd", ""), ("nhd_hnd", "&layout=hnd")):
+        r = _run("-u", f"kvx://local?prefill=1&decode=1&backend=sglang&isl=512&requests=4{extra}", "-m", M1B, "-o", str(out), "-b", name)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        s = json.load(open(out / name / "results.json"))["summary"]
+        assert s["verified_bit_exact"] is True and s["requests_verified"] == 4
+
+
+@pytest.mark.gpu
+def test_runner_routes_and_release_accounting(tmp_path):
+    """2P2D: spread routing (each decode replica reads both prefill replicas) and the router's bookings on a
+    bursty stream; every prefill rank must see one release per request it served, from the right consumer."""
+    out = tmp_path / "r"
+    r = _run("-u", "kvx://local?prefill=2&decode=2&isl=256,512&requests=6&route=spread&concurrency=2", "-m", M1B, "-o", str(out), "-b", "spread")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    res = json.load(open(out / "spread" / "results.json"))
+    s = res["summary"]
+    assert s["verified_bit_exact"] is True and s["requests_verified"] == 12 and s["releases_observed"] == s["releases_expected"] == 12
+    assert {q["prefill_replica"] for q in res["decode_ranks"][0]["requests"]} == {0, 1}
+    r = _run("-u", "kvx://local?prefill=2&decode=2&isl=256,2048&requests=10&arrival=bursty&gap_ms=0.2&route=sched", "-m", M1B,
+             "-o", str(out), "-b", "sched")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    s = json.load(open(out / "sched" / "results.json"))["summary"]
+    assert s["verified_bit_exact"] is True and s["requests_verified"] == s["requests"] == 10 and s["arrival_driven"] is True
+
+
+@pytest.mark.gpu
+def test_runner_layerwise_handoff(tmp_path):
+    """Layer-wise handoff through the worker API (publish_layers / pull_layers): 4 layer groups behind a
+    synthetic prefill, also with TP fan-in (each decode rank gated by two prefill ranks' flags)."""
+    out = tmp_path / "r"
+    for name, extra in (("lw", ""), ("lw_tp", "&ptp=4&dtp=2")):
+        r = _run("-u", f"kvx://local?prefill=1&decode=1&isl=512&requests=3&layerwise=4&prefill_ms=2{extra}", "-m", M1B, "-o", str(out), "-b", name)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        res = json.load(open(out / name / "results.json"))
+        assert res["summary"]["verified_bit_exact"] is True and res["summary"]["layerwise"] == 4
+        assert all(q["added_after_prefill_ms"] is not None and q["added_after_prefill_ms"] >= 0 for q in res["decode_ranks"][0]["requests"])
