@@ -413,6 +413,57 @@ def run_single(args):
             rec[name] = round(1e5 * (time.perf_counter() - t0), 1)
         short[str(s_isl)] = rec
 
+    # the same requests through the resident receiver (kvx_queue_*): no launch per request, the CTAs run from one
+    # request into the next.  Host wall clock from the first submit to the last request's completion word, per request
+    # ("stream": requests submitted back to back) and submit -> completion of ONE request at a time ("single"); next to
+    # them the per-request entry point measured the same way.
+    queue = {}
+    torch.cuda.synchronize()
+    with ctx.queue(P.pool, D.pool) as q:
+        for s_isl in (128, 1024, 2048, 4096, 8192):
+            m = shape.blocks_for(s_isl)
+            R = 16
+            ids = [(np.ascontiguousarray(perm_p[(j * m) % (sets * n - m):][:m]), np.ascontiguousarray(perm_d[(j * m) % (sets * n - m):][:m])) for j in range(R)]
+            word = torch.zeros(1, dtype=torch.int64).pin_memory()
+            b = m * shape.regions * shape.chunk_bytes()
+
+            def stream_q():
+                for a_, b_ in ids:
+                    t_ = q.submit(a_, b_, m)
+                q.wait(t_, 10000)
+
+            def single_q():
+                for a_, b_ in ids:
+                    q.wait(q.submit(a_, b_, m), 10000)
+
+            def stream_l():
+                for a_, b_ in ids:
+                    ctx.handoff_host(P.pool, a_, D.pool, b_, m, None, None, 1, None, stream)
+                stream.synchronize()
+
+            def single_l():
+                for a_, b_ in ids:
+                    ctx.handoff_host(P.pool, a_, D.pool, b_, m, None, None, 1, word, stream)
+                    stream.synchronize()
+
+            rec = {"requests": R, "payload_MiB_each": round(b / 2**20, 1)}
+            for name, fn in (("queue_stream_us", stream_q), ("queue_single_us", single_q), ("launch_stream_us", stream_l), ("launch_single_us", single_l)):
+                if name == "launch_stream_us":
+                    q.park()   # the launched kernels get the GPU to themselves (the idle receiver holds registers on every SM)
+                fn(); fn()
+                best = 1e9
+                for _ in range(5):
+                    t0 = time.perf_counter()
+                    fn()
+                    best = min(best, time.perf_counter() - t0)
+                rec[name] = round(1e6 * best / R, 2)
+            rec["queue_stream_hbm_frac_measured"] = round(2 * b / (rec["queue_stream_us"] * 1e-6) / 1e9 / hbm_peak, 4)
+            rec["launch_stream_hbm_frac_measured"] = round(2 * b / (rec["launch_stream_us"] * 1e-6) / 1e9 / hbm_peak, 4)
+            queue[str(s_isl)] = rec
+        queue["ctas"], queue["kernel_launches_for_all_of_the_above"] = q.ctas, q.launches
+        q.park()
+    torch.cuda.synchronize()
+
     # chunks of TP shards (Llama-3.1-70B, 80 layers, ISL 8192): 4, 2 and 1 KV heads per rank = 16, 8 and 4 KiB
     # chunks; small pieces switch the launch geometry (few consumer warps, more CTAs)
     shards = {}
@@ -462,7 +513,7 @@ def run_single(args):
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
                                    "oracle/kvx_oracle.c memcpy-per-row HND->NHD"},
         "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
-        "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "tp_shard_chunks": shards, "baselines": baselines,
+        "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "resident_queue": queue, "tp_shard_chunks": shards, "baselines": baselines,
         "options": {k: ctx.get_option(k) for k in kvx.OPT},
     }
     print(json.dumps(line))

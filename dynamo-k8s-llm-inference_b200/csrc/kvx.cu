@@ -103,6 +103,7 @@ struct kvx_ctx {
   };
   std::map<void*, Imported> imported;  // pointers handed out by import_record
   std::map<const void*, size_t> smem_limit;  // kernel → dynamic shared memory limit already set
+  std::vector<struct kvx_queue*> queues;      // resident receivers started on this context (stopped with it)
 };
 
 struct kvx_pool {
@@ -919,6 +920,7 @@ int32_t kvx_ctx_create(int32_t device, kvx_ctx** out) try {
 
 int32_t kvx_ctx_destroy(kvx_ctx* ctx) try {
   if (!ctx) return KVX_EINVAL;
+  while (!ctx->queues.empty()) kvx_queue_stop(ctx->queues.back());  // a resident kernel would block the sync below
   {
     DeviceGuard guard(ctx->device);
     if (guard.ok) {
@@ -1622,3 +1624,5 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
   if (bad(cudaGetLastError())) return KVX_ECUDA;
   return KVX_OK;
 } KVX_CATCH_ALL
+
+#include "kvx_queue_host.inl"

@@ -1,0 +1,361 @@
+// kvx_queue.cuh — the resident receiver: one persistent kernel per P→D edge that takes requests from a queue in
+// pinned host memory instead of being launched once per request.
+//
+// Why: a handoff of a short prompt is bounded by fixed costs, not bytes — the launch, the pipeline fill, and the
+// drain plus completion flag at the end (ISL 1k on one GPU: 45 us against 36 us of bytes).  A resident kernel pays
+// none of them between back-to-back requests: its CTAs walk from the last item of request k straight into the
+// first item of request k+1 with the shared-memory ring still full, and the completion of request k is counted
+// off the critical path.
+//
+// Structure of a CTA (blockDim = 32 * (2 + consumer warps)):
+//   warp 0   producer — exactly the producer of kvx_xfer_tma_kernel (table lookups 32 items at a time, cp.async.bulk
+//            into the mbarrier ring), in a loop over REQUESTS; it also counts this CTA's part of a request as done
+//            once the consumers have released the request's last stage
+//   warp 1   dispatcher — only in CTA 0: polls the host ring (ld.acquire.sys over PCIe), copies a new request's block
+//            ids into the device table ring, publishes it to all CTAs with one release store; decides when the kernel
+//            parks (see below)
+//   warps 2+ consumers — the consumers of kvx_xfer_tma_kernel (shared memory → permuted 16-byte stores), looping
+//            until they meet the exit marker
+//
+// Parking: a kernel that never ends would block every cudaDeviceSynchronize / cudaFree of the process.  After
+// `idle_ns` without a request the dispatcher parks the kernel: it writes seq+1 to the host word `parked`, fences,
+// and looks at the host ring ONCE MORE; only if that is still empty does it publish the park to the CTAs and exit.
+// The host does the mirror image on submit (write the slot, full fence, read `parked`; if set, clear it and launch
+// the kernel again on the queue's stream).  Either the kernel sees the slot or the host sees `parked` — or both, and
+// then the extra launch starts where the previous one parked (device-resident `start`), finds nothing to do and parks again.
+#pragma once
+#include "kvx_kernels.cuh"
+
+namespace kvx {
+
+constexpr unsigned kQueueExit = 0xffffffffu;  // stage marker: consumers leave
+
+struct QueueDesc {  // one request as published to the CTAs (device memory)
+  unsigned int n, tab_off, total_items, reserved;
+  unsigned long long flag, flag_val, done;  // flag / done: addresses to receive flag_val (0 = none)
+  unsigned long long seq1;                  // seq + 1 (what the per-slot host completion word receives)
+};
+
+struct QueueHostSlot {  // one request as submitted by the host (pinned host memory, 64 bytes)
+  unsigned long long seq1;  // seq + 1 of the request in this slot; written LAST by the host
+  unsigned int n, tab_off;  // blocks; first entry of [src ids n][dst ids n] in the table rings
+  unsigned long long flag, flag_val, done;
+  unsigned long long pad[3];
+};
+static_assert(sizeof(QueueHostSlot) == 64, "one slot = one 64-byte line");
+
+struct QueueParams {
+  XferParams x;                  // the edge's geometry (plan, strides, region bases); n, total_items, tables per request
+  QueueDesc* desc;               // device [ring]
+  int* tables;                   // device table ring [table_ring]
+  unsigned int* done_cnt;        // device [ring]: CTAs that finished the request in this slot
+  unsigned long long* pub_seq;   // device: requests published to the CTAs so far
+  unsigned long long* park;      // device: (generation << 40) | seq, set when the launch of that generation parks
+  unsigned long long* start;     // device [2]: the launch of generation g starts at start[g & 1] (never written while
+                                 // g runs) and leaves where it parked in start[(g + 1) & 1] for generation g + 1
+  const QueueHostSlot* h_slots;  // pinned host ring, through its device alias
+  const int* h_tables;           // pinned host table ring
+  unsigned long long* h_done;    // pinned host [ring]: seq+1 once the request in that slot has landed
+  unsigned long long* h_parked;  // pinned host: seq+1 at which the kernel parked (host clears it on relaunch)
+  const unsigned int* h_stop;    // pinned host: 1 = park at once
+  unsigned int ring_mask, items_per_block;  // ring size - 1; regions * pieces per chunk
+  unsigned int gen, pad;
+  unsigned long long idle_ns;
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Block ids of the request being served: the device table ring.  It is rewritten while the kernel lives, so the
+// loads go to L2 (relaxed, gpu scope), never through the non-coherent path.
+struct TabQueue {
+  const int* tab;
+  __device__ __forceinline__ int get(const XferSide& s, unsigned blk) const {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(tab + s.tab_off + blk));
+    return v;
+  }
+};
+
+// ---- dispatcher (CTA 0, warp 1) ----------------------------------------------------------------------------
+__device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned lane) {
+  unsigned long long seq = q.start[q.gen & 1u];
+  unsigned long long t_idle = global_timer_ns();
+  for (;;) {
+    const QueueHostSlot* hs = q.h_slots + (seq & q.ring_mask);
+    unsigned long long have = 0;
+    if (lane == 0) have = ld_acquire_sys(&hs->seq1);
+    have = __shfl_sync(0xffffffffu, have, 0);
+    if (have == seq + 1) {
+      // the slot's other fields were written before seq1 (host release) and are read after it (acquire)
+      unsigned n = 0, tab_off = 0;
+      unsigned long long flag = 0, val = 0, done = 0;
+      if (lane == 0) {
+        const volatile QueueHostSlot* v = hs;
+        n = v->n; tab_off = v->tab_off; flag = v->flag; val = v->flag_val; done = v->done;
+      }
+      n = __shfl_sync(0xffffffffu, n, 0);
+      tab_off = __shfl_sync(0xffffffffu, tab_off, 0);
+      // both id lists, [src n][dst n], padded to 16 bytes by the host: host ring → device ring, same offset
+      const unsigned quads = (2u * n + 3u) / 4u;
+      const int4* src = reinterpret_cast<const int4*>(q.h_tables + tab_off);
+      int4* dst = reinterpret_cast<int4*>(q.tables + tab_off);
+      for (unsigned i = lane; i < quads; i += 32u) {
+        int4 v;
+        asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i));
+        dst[i] = v;
+      }
+      if (lane == 0) {
+        QueueDesc* d = q.desc + (seq & q.ring_mask);
+        d->n = n; d->tab_off = tab_off; d->total_items = n * q.items_per_block;
+        d->flag = flag; d->flag_val = val; d->done = done; d->seq1 = seq + 1;
+      }
+      __threadfence();  // every lane's table stores and lane 0's descriptor, before the publication
+      __syncwarp();
+      if (lane == 0) st_release_gpu(q.pub_seq, seq + 1);
+      ++seq;
+      t_idle = global_timer_ns();
+      continue;
+    }
+    unsigned stop = 0;
+    if (lane == 0) stop = *reinterpret_cast<const volatile unsigned int*>(q.h_stop);
+    stop = __shfl_sync(0xffffffffu, stop, 0);
+    if (stop != 0 || global_timer_ns() - t_idle > q.idle_ns) {
+      unsigned long long again = 0;
+      if (lane == 0) {
+        st_release_sys(q.h_parked, seq + 1);
+        __threadfence_system();
+        again = ld_acquire_sys(&hs->seq1);
+      }
+      again = __shfl_sync(0xffffffffu, again, 0);
+      if (again == seq + 1 && stop == 0) {  // a request slipped in between the last look and the announcement
+        t_idle = global_timer_ns();
+        continue;
+      }
+      if (lane == 0) {
+        q.start[(q.gen + 1u) & 1u] = seq;
+        __threadfence();
+        st_release_gpu(q.park, (static_cast<unsigned long long>(q.gen) << 40) | seq);
+      }
+      return;
+    }
+    __nanosleep(200);
+  }
+}
+
+// A published descriptor, read past L1 (the slot is rewritten while the kernel lives).
+__device__ __forceinline__ QueueDesc load_desc(const QueueDesc* p) {
+  const volatile QueueDesc* v = p;
+  QueueDesc d;
+  d.n = v->n; d.tab_off = v->tab_off; d.total_items = v->total_items; d.reserved = 0;
+  d.flag = v->flag; d.flag_val = v->flag_val; d.done = v->done; d.seq1 = v->seq1;
+  return d;
+}
+
+// One CTA's share of request `d` is done (all its stores are visible to this thread through the ring's barriers):
+// publish them, count, and let the last CTA deliver the request's notifications.
+__device__ __forceinline__ void queue_count_done(const QueueParams& q, const QueueDesc& d, unsigned slot) {
+  if (q.x.data_local) __threadfence(); else __threadfence_system();
+  const unsigned prev = atomicAdd(q.done_cnt + slot, 1u);
+  if (prev == gridDim.x - 1) {
+    q.done_cnt[slot] = 0u;
+    __threadfence_system();
+    if (d.flag != 0) st_relaxed_sys(reinterpret_cast<unsigned long long*>(d.flag), d.flag_val);
+    if (d.done != 0) st_relaxed_sys(reinterpret_cast<unsigned long long*>(d.done), d.flag_val);
+    st_relaxed_sys(q.h_done + slot, d.seq1);
+  }
+}
+
+template <int KMAX>
+__global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
+  constexpr int VEC = 16;
+  extern __shared__ __align__(1024) unsigned char stage_mem[];
+  __shared__ __align__(8) unsigned long long full_bar[kMaxStages];
+  __shared__ __align__(8) unsigned long long empty_bar[kMaxStages];
+  __shared__ unsigned long long meta_dst[kMaxStages];
+  __shared__ unsigned int meta_bytes[kMaxStages];
+
+  const XferParams& p = q.x;
+  const unsigned tid = threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const unsigned warp = tid >> 5;
+  const unsigned cons_warps = (blockDim.x >> 5) - 2u;
+  const unsigned S = p.stages;
+  if (tid == 0) {
+    for (unsigned s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1u);
+      mbar_init(&empty_bar[s], cons_warps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const unsigned bid = blockIdx.x;
+  const unsigned grid = gridDim.x;
+
+  if (warp == 1) {
+    if (bid == 0) queue_dispatch(q, lane);
+    return;
+  }
+  if (warp == 0) {
+    // ------------------------------ producer: a loop over requests ------------------------------
+    // Completions wait in a FIFO until the consumers have released the request's last stage; an entry is always
+    // popped before its stage is filled again (the drain right after every wait for a free stage), so the
+    // barrier's parity cannot wrap under it.
+    struct Pending { unsigned slot, stage, parity; };
+    Pending pend[kMaxStages + 1];
+    unsigned pend_head = 0, pend_n = 0;
+    auto drain = [&](bool block) {
+      while (pend_n != 0) {
+        const Pending e = pend[pend_head];
+        if (block) mbar_wait(&empty_bar[e.stage], e.parity);
+        else if (!mbar_try_wait(&empty_bar[e.stage], e.parity)) break;
+        if (lane == 0) {
+          const QueueDesc d = load_desc(q.desc + e.slot);
+          queue_count_done(q, d, e.slot);
+        }
+        pend_head = (pend_head + 1u) % (kMaxStages + 1u);
+        --pend_n;
+      }
+    };
+    unsigned long long seq = q.start[q.gen & 1u];
+    unsigned s = 0, phase = 0;
+    for (;;) {
+      // wait for request `seq`, or for the park
+      bool leave = false;
+      for (;;) {
+        unsigned long long pub = 0, pk = 0;
+        if (lane == 0) {
+          pub = ld_acquire_gpu(q.pub_seq);
+          pk = ld_acquire_gpu(q.park);
+        }
+        pub = __shfl_sync(0xffffffffu, pub, 0);
+        pk = __shfl_sync(0xffffffffu, pk, 0);
+        if (pub > seq) break;
+        drain(false);
+        if ((pk >> 40) == q.gen && seq >= (pk & ((1ull << 40) - 1))) { leave = true; break; }
+        __nanosleep(100);
+      }
+      if (leave) break;
+      const unsigned slot = static_cast<unsigned>(seq & q.ring_mask);
+      unsigned dn = 0, dtab = 0, dtotal = 0;
+      if (lane == 0) {
+        const volatile QueueDesc* d = q.desc + slot;
+        dn = d->n; dtab = d->tab_off; dtotal = d->total_items;
+      }
+      dn = __shfl_sync(0xffffffffu, dn, 0);
+      dtab = __shfl_sync(0xffffffffu, dtab, 0);
+      dtotal = __shfl_sync(0xffffffffu, dtotal, 0);
+      XferParams rp = p;  // this request's view of the edge
+      rp.n = dn; rp.total_items = dtotal;
+      rp.src.tab_off = dtab; rp.dst.tab_off = dtab + dn;
+      const TabQueue tab{q.tables};
+      const unsigned my_items = bid < dtotal ? (dtotal - bid + grid - 1u) / grid : 0u;
+      unsigned last_stage = 0, last_parity = 0;
+      RawItem raw{};
+      if (lane < my_items) item_load(rp, tab, bid + lane * grid, raw);
+      for (unsigned base = 0; base < my_items; base += 32u) {
+        unsigned long long sa = 0, da = 0;
+        unsigned bytes = 0;
+        if (base + lane < my_items) item_finish(rp, raw, sa, da, bytes);
+        if (base + 32u + lane < my_items) item_load(rp, tab, bid + (base + 32u + lane) * grid, raw);
+        const unsigned cnt = min(32u, my_items - base);
+        for (unsigned j = 0; j < cnt; ++j) {
+          const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
+          const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
+          const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
+          mbar_wait(&empty_bar[s], phase ^ 1u);
+          drain(false);
+          unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+          if (lane == 0) {
+            meta_dst[s] = dst;
+            meta_bytes[s] = nbytes;
+            mbar_arrive_expect_tx(&full_bar[s], nbytes);
+          }
+          __syncwarp();
+          if (nbytes != 0) {
+            if (p.s_runs == 1u) {
+              if (lane == 0) bulk_g2s(stage, src, nbytes, &full_bar[s]);
+            } else {
+              for (unsigned x = lane; x < p.s_runs; x += 32u)
+                bulk_g2s(stage + x * p.s_run_bytes, src + static_cast<unsigned long long>(x) * p.s_stride, p.s_run_bytes,
+                         &full_bar[s]);
+            }
+          }
+          last_stage = s; last_parity = phase;
+          if (++s == S) { s = 0; phase ^= 1u; }
+        }
+      }
+      if (my_items == 0) {
+        if (lane == 0) {  // nothing of this request falls to this CTA: it still counts
+          const QueueDesc d = load_desc(q.desc + slot);
+          queue_count_done(q, d, slot);
+        }
+      } else {
+        pend[(pend_head + pend_n) % (kMaxStages + 1u)] = Pending{slot, last_stage, last_parity};
+        ++pend_n;
+      }
+      ++seq;
+    }
+    drain(true);
+    // exit marker for the consumers
+    mbar_wait(&empty_bar[s], phase ^ 1u);
+    if (lane == 0) {
+      meta_bytes[s] = kQueueExit;
+      mbar_arrive_expect_tx(&full_bar[s], 0u);
+    }
+    return;
+  }
+  // ------------------------------ consumers ------------------------------
+  const unsigned ctid = tid - 64u;
+  const unsigned T = blockDim.x - 64u;
+  unsigned doff[KMAX];
+  const unsigned upr = p.d_run_bytes / VEC;
+#pragma unroll
+  for (int k = 0; k < KMAX; ++k) {
+    const unsigned u = ctid + k * T;
+    doff[k] = dst_run_offset(p, u / upr) + (u % upr) * VEC;
+  }
+  unsigned s = 0, phase = 0;
+  for (;;) {
+    // an idle queue keeps the consumers here until the park (bounded by idle_ns, far below mbar_wait's trap)
+    mbar_wait(&full_bar[s], phase);
+    const unsigned nbytes = meta_bytes[s];
+    if (nbytes == kQueueExit) break;
+    const unsigned long long dst = meta_dst[s];
+    const unsigned units = nbytes / VEC;
+    const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+    Vec<VEC> v[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      const unsigned u = ctid + k * T;
+      if (u < units) lds_vec(v[k], stage + static_cast<size_t>(u) * VEC);
+    }
+#pragma unroll
+    for (int k = 0; k < KMAX; ++k) {
+      const unsigned u = ctid + k * T;
+      if (u < units) stg_stream(dst + doff[k], v[k]);
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&empty_bar[s]);
+    if (++s == S) { s = 0; phase ^= 1u; }
+  }
+}
+
+}  // namespace kvx

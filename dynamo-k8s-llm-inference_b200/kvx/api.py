@@ -256,6 +256,10 @@ class Context:
                                               _ptr(h_done), _stream(stream)), "kvx_handoff_host")
 
 
+    def queue(self, src: Pool, dst: Pool, xf: Optional[Xform] = None, *, max_ctas: int = 0, idle_us: int = 0) -> "Queue":
+        """Start a resident receiver for the edge src → dst (kvx_queue_start)."""
+        return Queue(self, src, dst, xf, max_ctas=max_ctas, idle_us=idle_us)
+
     def handoff_batch(self, src: Pool, dst: Pool, requests, xf: Optional[Xform] = None, stream=None) -> None:
         """Several requests between the same two pools in one launch (kvx_handoff_batch).  `requests` is a
         sequence of (h_src_ids, h_dst_ids, flag, flag_val, h_done): int32 numpy arrays (or None for an empty
@@ -275,6 +279,70 @@ class Context:
         x = xf.c() if xf else None
         self._check(self.lib.kvx_handoff_batch(self.handle, src.handle, dst.handle, arr, len(requests),
                                                ctypes.byref(x) if x else None, _stream(stream)), "kvx_handoff_batch")
+
+
+class Queue:
+    """kvx_queue: the resident receiver of one P→D edge.  A persistent kernel serves requests from a queue in
+    pinned host memory: submit() costs a few hundred nanoseconds and never launches while the kernel is resident;
+    back-to-back requests run into each other without draining the pipeline.  The kernel parks (exits) after
+    `idle_us` without work and comes back with the next submit; park() makes it leave now — do that before
+    anything that waits for the whole device (torch.cuda.synchronize, cudaFree) if you cannot afford to wait out
+    the idle time."""
+
+    def __init__(self, ctx: "Context", src: Pool, dst: Pool, xf: Optional[Xform] = None, *, max_ctas: int = 0,
+                 idle_us: int = 0):
+        self.ctx = ctx
+        x = xf.c() if xf else None
+        h = c_vp()
+        ctx._check(ctx.lib.kvx_queue_start(ctx.handle, src.handle, dst.handle, ctypes.byref(x) if x else None, max_ctas,
+                                           idle_us, ctypes.byref(h)), "kvx_queue_start")
+        self.handle = h.value
+
+    def submit(self, h_src_table, h_dst_table, n: Optional[int] = None, flag: Optional[int] = None, flag_val: int = 1,
+               h_done=None) -> int:
+        """Hand over one request (int32 numpy arrays / pinned tensors of block ids); returns its ticket."""
+        if n is None:
+            n = 0 if h_dst_table is None else len(h_dst_table)
+        t = c_u64()
+        self.ctx._check(self.ctx.lib.kvx_queue_submit(self.handle, _ptr(h_src_table), _ptr(h_dst_table), n, flag, flag_val,
+                                                      _ptr(h_done), ctypes.byref(t)), "kvx_queue_submit")
+        return t.value
+
+    def wait(self, ticket: int, timeout_ms: int = 5000) -> None:
+        self.ctx._check(self.ctx.lib.kvx_queue_wait(self.handle, ticket, timeout_ms), "kvx_queue_wait")
+
+    def poll(self, ticket: int) -> bool:
+        rc = self.ctx.lib.kvx_queue_poll(self.handle, ticket)
+        if rc == ENOTREADY:
+            return False
+        self.ctx._check(rc, "kvx_queue_poll")
+        return True
+
+    def park(self) -> None:
+        self.ctx._check(self.ctx.lib.kvx_queue_park(self.handle), "kvx_queue_park")
+
+    @property
+    def launches(self) -> int:
+        n, c = c_u64(), c_u32()
+        self.ctx._check(self.ctx.lib.kvx_queue_launch_count(self.handle, ctypes.byref(n), ctypes.byref(c)), "kvx_queue_launch_count")
+        return n.value
+
+    @property
+    def ctas(self) -> int:
+        n, c = c_u64(), c_u32()
+        self.ctx._check(self.ctx.lib.kvx_queue_launch_count(self.handle, ctypes.byref(n), ctypes.byref(c)), "kvx_queue_launch_count")
+        return c.value
+
+    def stop(self) -> None:
+        if self.handle:
+            self.ctx._check(self.ctx.lib.kvx_queue_stop(self.handle), "kvx_queue_stop")
+            self.handle = None
+
+    def __enter__(self) -> "Queue":
+        return self
+
+    def __exit__(self, *exc) -> None:
+        self.stop()
 
 
 STATIC_MAX_BLOCKS = 4096

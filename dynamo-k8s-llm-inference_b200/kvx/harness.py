@@ -355,151 +355,172 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
         ids_of_p = {pr: prefill_ids(pr) for pr in p_reps}
         remote_ids = [ids_of_p[r.p_rep][r.p_serial] for r in mine]
         local_ids = _pre_allocate(nb, [r.n for r in mine], SEED + 13 + 100 * me.replica, hold)  # same on all TP ranks of a replica
-        ver = _Verifier(torch, w, shape, nb, me, sources, p_tp, d_tp, hp, p_layouts) if cfg.verify else None
-        lanes = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in mine]
-        ev_ready = [torch.cuda.Event(enable_timing=True) for _ in mine]  # gated streams: last layer group is ready
-        gated = G > 1 or cfg.prefill_ms > 0   # the pulls wait on the GPU for the prefill worker's "layers ready" flags
-        t_sub, t_done, t_ready = [0.0] * len(mine), [0.0] * len(mine), [0.0] * len(mine)
-        group_of: Dict[int, Tuple[int, List[int]]] = {}
-        checked_args: List[object] = [None] * len(mine)
-        # checks run on the verifier's stream in the order requests LAND; before request i reuses the blocks of
-        # requests <= i - hold - 1, every one of their checks must have read them: wait for the latest-queued of them
-        chk_events: List[object] = []
-        chk_pos: List[Optional[int]] = [None] * len(mine)
-        prefix = {"upto": -1, "pos": -1}
+        served_on = {pr: len(_served_by(per_d, pr)) for pr in p_reps}  # flag values grow from pass to pass
 
-        def wait_for_checks(i: int, streams) -> None:
-            limit = i - hold - 1
-            if ver is None or limit < 0:
-                return
-            while prefix["upto"] < limit:
-                prefix["upto"] += 1
-                prefix["pos"] = max(prefix["pos"], chk_pos[prefix["upto"]])
-            for s_ in streams:
-                s_.wait_event(chk_events[prefix["pos"]])
+        def run_pass(pass_idx: int, ver):
+            """One run of the whole stream.  `ver` = the verifier that checks every request as it lands (the
+            verification pass), or None (the timed pass: nothing but the transfers touches the GPU)."""
+            val_of = lambda r: pass_idx * served_on[r.p_rep] + r.p_serial + 1  # noqa: E731
+            lanes = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in mine]
+            ev_ready = [torch.cuda.Event(enable_timing=True) for _ in mine]  # gated streams: last layer group is ready
+            gated = G > 1 or cfg.prefill_ms > 0   # the pulls wait on the GPU for the prefill worker's "layers ready" flags
+            t_sub, t_done, t_ready = [0.0] * len(mine), [0.0] * len(mine), [0.0] * len(mine)
+            group_of: Dict[int, Tuple[int, List[int]]] = {}
+            checked_args: List[object] = [None] * len(mine)
+            # checks run on the verifier's stream in the order requests LAND; before request i reuses the blocks of
+            # requests <= i - hold - 1, every one of their checks must have read them: wait for the latest-queued of them
+            chk_events: List[object] = []
+            chk_pos: List[Optional[int]] = [None] * len(mine)
+            prefix = {"upto": -1, "pos": -1}
 
-        def remote_of(i: int) -> Dict[int, np.ndarray]:
-            return {mine[i].p_rep * 1000 + e.p_rank: remote_ids[i] for e in srcs}
+            def wait_for_checks(i: int, streams) -> None:
+                limit = i - hold - 1
+                if ver is None or limit < 0:
+                    return
+                while prefix["upto"] < limit:
+                    prefix["upto"] += 1
+                    prefix["pos"] = max(prefix["pos"], chk_pos[prefix["upto"]])
+                for s_ in streams:
+                    s_.wait_event(chk_events[prefix["pos"]])
 
-        def edges_of(i: int) -> Dict[int, object]:
-            return {mine[i].p_rep * 1000 + e.p_rank: e for e in srcs}
+            def remote_of(i: int) -> Dict[int, np.ndarray]:
+                return {mine[i].p_rep * 1000 + e.p_rank: remote_ids[i] for e in srcs}
 
-        def flag_slot(i: int, e) -> int:
-            cons = consumers_of(e.p_rank)
-            return _release_slot(mine[i].p_serial, cons.index(me.tp_rank), len(cons), w.remotes[mine[i].p_rep * 1000 + e.p_rank].meta.num_flags)
+            def edges_of(i: int) -> Dict[int, object]:
+                return {mine[i].p_rep * 1000 + e.p_rank: e for e in srcs}
 
-        def issue(i: int, lane) -> None:
-            """Queue request i on a lane: one pull per source edge (fan-in when p_tp > d_tp), joined on lane[0]."""
-            r = mine[i]
-            wait_for_checks(i, lane)
-            ev[i][0].record(lane[0])
-            for j, e in enumerate(srcs):
-                if j:
-                    lane[j].wait_event(ev[i][0])
-                key = r.p_rep * 1000 + e.p_rank
-                edge = e if (p_tp != d_tp) else None
-                if gated:
-                    for g in range(G):
-                        w.wait(w.layer_ready_slot(r.p_serial, g, G, w.num_flags, j, len(srcs)), r.p_serial + 1, 60000, lane[j])
-                        if g == G - 1 and j == 0:
-                            ev_ready[i].record(lane[0])
-                        w.pull_layers(key, remote_ids[i], local_ids[i], g, G,
-                                      notify_slot=flag_slot(i, e) if g == G - 1 else None, value=r.p_serial + 1,
-                                      edge=edge, stream=lane[j])
-                else:
-                    w.pull(key, remote_ids[i], local_ids[i], notify_slot=flag_slot(i, e), value=r.p_serial + 1,
-                           edge=edge, host_tables=True, stream=lane[j])
-            for j in range(1, len(srcs)):
-                done_j = torch.cuda.Event()
-                done_j.record(lane[j])
-                lane[0].wait_event(done_j)
-            ev[i][1].record(lane[0])
+            def flag_slot(i: int, e) -> int:
+                cons = consumers_of(e.p_rank)
+                return _release_slot(mine[i].p_serial, cons.index(me.tp_rank), len(cons), w.remotes[mine[i].p_rep * 1000 + e.p_rank].meta.num_flags)
 
-        def landed(i: int) -> None:
-            if ver is not None:
-                chk_events.append(ver.check_request(ev[i][1], remote_of(i), local_ids[i], edges_of(i),
-                                                    corrupt=cfg.corrupt is not None and tuple(cfg.corrupt) == (me.replica, i)))
-                chk_pos[i] = len(chk_events) - 1
-            checked_args[i] = (remote_of(i), local_ids[i], edges_of(i))
+            def issue(i: int, lane) -> None:
+                """Queue request i on a lane: one pull per source edge (fan-in when p_tp > d_tp), joined on lane[0]."""
+                r = mine[i]
+                wait_for_checks(i, lane)
+                ev[i][0].record(lane[0])
+                for j, e in enumerate(srcs):
+                    if j:
+                        lane[j].wait_event(ev[i][0])
+                    key = r.p_rep * 1000 + e.p_rank
+                    edge = e if (p_tp != d_tp) else None
+                    if gated:
+                        for g in range(G):
+                            w.wait(w.layer_ready_slot(r.p_serial, g, G, w.num_flags, j, len(srcs)), val_of(r), 60000, lane[j])
+                            if g == G - 1 and j == 0:
+                                ev_ready[i].record(lane[0])
+                            w.pull_layers(key, remote_ids[i], local_ids[i], g, G,
+                                          notify_slot=flag_slot(i, e) if g == G - 1 else None, value=val_of(r),
+                                          edge=edge, stream=lane[j])
+                    else:
+                        w.pull(key, remote_ids[i], local_ids[i], notify_slot=flag_slot(i, e), value=val_of(r),
+                               edge=edge, host_tables=True, stream=lane[j])
+                for j in range(1, len(srcs)):
+                    done_j = torch.cuda.Event()
+                    done_j.record(lane[j])
+                    lane[0].wait_event(done_j)
+                ev[i][1].record(lane[0])
 
-        dist.barrier(group=group)
-        torch.cuda.synchronize()
-        t_begin = time.perf_counter()
-        now_ms = lambda: 1e3 * (time.perf_counter() - t_begin)  # noqa: E731
-        batch = cfg.batch if (cfg.batch > 1 and len(srcs) == 1 and p_tp == d_tp and cfg.route == "pair"
-                              and cfg.ready_ms is None and G == 1) else 1
-        if batch > 1:
-            # one scheduler step = up to `batch` queued requests, received in one launch; closed loop over steps
-            lane0 = lanes[0][0]
-            for g0 in range(0, len(mine), batch):
-                qs = list(range(g0, min(len(mine), g0 + batch)))
-                key = mine[g0].p_rep * 1000 + srcs[0].p_rank
-                wait_for_checks(g0, [lane0])
-                t0 = time.perf_counter()
-                ev[g0][0].record(lane0)
-                w.pull_many(key, [(remote_ids[i], local_ids[i], flag_slot(i, srcs[0]), mine[i].p_serial + 1, None) for i in qs],
-                            stream=lane0)
-                ev[g0][1].record(lane0)
-                ev[g0][1].synchronize()
-                t1 = time.perf_counter()
-                for i in qs:
-                    t_sub[i], t_done[i], group_of[i] = t0, t1, (g0, qs)
-                    ev[i] = ev[g0]
-                    landed(i)
-        else:
-            # at most c requests in flight, each on a lane of its own; a request becomes eligible when its KV is
-            # ready (arrival-driven) or at once (closed loop); FIFO in the planned order
-            nxt, inflight, free_lanes = 0, {}, list(range(c))
-            while nxt < len(mine) or inflight:
-                progressed = False
-                for i in list(inflight):
-                    if ev[i][1].query():
-                        t_done[i] = time.perf_counter()
-                        free_lanes.append(inflight.pop(i))
+            def landed(i: int) -> None:
+                if ver is not None:
+                    chk_events.append(ver.check_request(ev[i][1], remote_of(i), local_ids[i], edges_of(i),
+                                                        corrupt=cfg.corrupt is not None and tuple(cfg.corrupt) == (me.replica, i)))
+                    chk_pos[i] = len(chk_events) - 1
+                checked_args[i] = (remote_of(i), local_ids[i], edges_of(i))
+
+            dist.barrier(group=group)
+            torch.cuda.synchronize()
+            t_begin = time.perf_counter()
+            now_ms = lambda: 1e3 * (time.perf_counter() - t_begin)  # noqa: E731
+            batch = cfg.batch if (cfg.batch > 1 and len(srcs) == 1 and p_tp == d_tp and cfg.route == "pair"
+                                  and cfg.ready_ms is None and G == 1) else 1
+            if batch > 1:
+                # one scheduler step = up to `batch` queued requests, received in one launch; closed loop over steps
+                lane0 = lanes[0][0]
+                for g0 in range(0, len(mine), batch):
+                    qs = list(range(g0, min(len(mine), g0 + batch)))
+                    key = mine[g0].p_rep * 1000 + srcs[0].p_rank
+                    wait_for_checks(g0, [lane0])
+                    t0 = time.perf_counter()
+                    ev[g0][0].record(lane0)
+                    w.pull_many(key, [(remote_ids[i], local_ids[i], flag_slot(i, srcs[0]), val_of(mine[i]), None) for i in qs],
+                                stream=lane0)
+                    ev[g0][1].record(lane0)
+                    ev[g0][1].synchronize()
+                    t1 = time.perf_counter()
+                    for i in qs:
+                        t_sub[i], t_done[i], group_of[i] = t0, t1, (g0, qs)
+                        ev[i] = ev[g0]
                         landed(i)
-                        progressed = True
-                while nxt < len(mine) and free_lanes and (mine[nxt].ready_ms is None or mine[nxt].ready_ms <= now_ms()):
-                    lane_id = free_lanes.pop(0)
-                    t_sub[nxt] = time.perf_counter()
-                    t_ready[nxt] = t_begin + (mine[nxt].ready_ms or 0.0) / 1e3 if mine[nxt].ready_ms is not None else t_sub[nxt]
-                    issue(nxt, lanes[lane_id])
-                    inflight[nxt] = lane_id
-                    nxt += 1
-                    progressed = True
-                if not progressed and not inflight and nxt < len(mine):
-                    wait = mine[nxt].ready_ms - now_ms()
-                    if wait > 0.2:
-                        time.sleep((wait - 0.1) / 1e3)
-        torch.cuda.synchronize()
-        t_end = time.perf_counter()
-        w.ctx.check()
-        per_req = []
-        for i, r in enumerate(mine):
-            b = r.n * shape.regions * chunk_d
-            if i in group_of:  # batched: the step's requests complete together; rate = the step's bytes over its time
-                g0, qs = group_of[i]
-                xfer = ev[g0][0].elapsed_time(ev[g0][1]) / 1e3
-                rate = sum(mine[x].n for x in qs) * shape.regions * chunk_d / xfer / 1e9
-                ttft = 1e3 * (t_done[i] - t_sub[i])
             else:
-                xfer = ev[i][0].elapsed_time(ev[i][1]) / 1e3
-                rate = b / xfer / 1e9 if xfer > 0 else 0.0
-                ttft = 1e3 * (t_done[i] - t_ready[i])
-            after_prefill = ev_ready[i].elapsed_time(ev[i][1]) if (gated and i not in group_of) else None
-            per_req.append({"request": r.q, "added_after_prefill_ms": after_prefill, "isl": r.isl, "num_blocks": r.n, "bytes_transferred": b, "prefill_replica": r.p_rep,
-                            "num_descriptors": r.n * shape.regions * len(srcs), "xfer_time_seconds": xfer,
-                            "throughput_GBps": rate, "batched_with": len(group_of[i][1]) if i in group_of else 1,
-                            "ready_ms": r.ready_ms, "queued_ms": 1e3 * (t_sub[i] - t_ready[i]) if i not in group_of else 0.0,
-                            "time_to_first_token_added_ms": ttft})
-        verdict = ver.finish([a_ for a_ in checked_args if a_ is not None]) if ver is not None else None
+                # at most c requests in flight, each on a lane of its own; a request becomes eligible when its KV is
+                # ready (arrival-driven) or at once (closed loop); FIFO in the planned order
+                nxt, inflight, free_lanes = 0, {}, list(range(c))
+                while nxt < len(mine) or inflight:
+                    progressed = False
+                    for i in list(inflight):
+                        if ev[i][1].query():
+                            t_done[i] = time.perf_counter()
+                            free_lanes.append(inflight.pop(i))
+                            landed(i)
+                            progressed = True
+                    while nxt < len(mine) and free_lanes and (mine[nxt].ready_ms is None or mine[nxt].ready_ms <= now_ms()):
+                        lane_id = free_lanes.pop(0)
+                        t_sub[nxt] = time.perf_counter()
+                        t_ready[nxt] = t_begin + (mine[nxt].ready_ms or 0.0) / 1e3 if mine[nxt].ready_ms is not None else t_sub[nxt]
+                        issue(nxt, lanes[lane_id])
+                        inflight[nxt] = lane_id
+                        nxt += 1
+                        progressed = True
+                    if not progressed and not inflight and nxt < len(mine):
+                        wait = mine[nxt].ready_ms - now_ms()
+                        if wait > 0.2:
+                            time.sleep((wait - 0.1) / 1e3)
+            torch.cuda.synchronize()
+            t_end = time.perf_counter()
+            w.ctx.check()
+            per_req = []
+            for i, r in enumerate(mine):
+                b = r.n * shape.regions * chunk_d
+                if i in group_of:  # batched: the step's requests complete together; rate = the step's bytes over its time
+                    g0, qs = group_of[i]
+                    xfer = ev[g0][0].elapsed_time(ev[g0][1]) / 1e3
+                    rate = sum(mine[x].n for x in qs) * shape.regions * chunk_d / xfer / 1e9
+                    ttft = 1e3 * (t_done[i] - t_sub[i])
+                else:
+                    xfer = ev[i][0].elapsed_time(ev[i][1]) / 1e3
+                    rate = b / xfer / 1e9 if xfer > 0 else 0.0
+                    ttft = 1e3 * (t_done[i] - t_ready[i])
+                after_prefill = ev_ready[i].elapsed_time(ev[i][1]) if (gated and i not in group_of) else None
+                per_req.append({"request": r.q, "added_after_prefill_ms": after_prefill, "isl": r.isl, "num_blocks": r.n, "bytes_transferred": b, "prefill_replica": r.p_rep,
+                                "num_descriptors": r.n * shape.regions * len(srcs), "xfer_time_seconds": xfer,
+                                "throughput_GBps": rate, "batched_with": len(group_of[i][1]) if i in group_of else 1,
+                                "ready_ms": r.ready_ms, "queued_ms": 1e3 * (t_sub[i] - t_ready[i]) if i not in group_of else 0.0,
+                                "time_to_first_token_added_ms": ttft})
+            return per_req, t_end - t_begin, [a_ for a_ in checked_args if a_ is not None]
+
+        # Pass 0 is timed and runs nothing but the transfers; its final state is checked whole-pool.  Pass 1 repeats
+        # the identical stream (same ids, same order, same concurrency) into a canary-filled pool and compares every
+        # request with its source the moment it lands, which costs GPU time and therefore is not the timed pass.
+        per_req, wall, landed_args = run_pass(0, None)
+        ver = _Verifier(torch, w, shape, nb, me, sources, p_tp, d_tp, hp, p_layouts) if cfg.verify else None
+        verdict = None
+        if ver is not None:
+            timed_final = ver.finish(landed_args)
+            synth.fill_canary(w.kv)
+            torch.cuda.synchronize()
+            _, _, landed_args = run_pass(1, ver)
+            verdict = ver.finish(landed_args)
+            verdict["timed_pass_final_blocks_ok"] = timed_final["final_blocks_ok"]
+            verdict["timed_pass_canary_blocks_ok"] = timed_final["canary_blocks_ok"]
         ok = None
         if verdict is not None:
-            ok = (verdict["requests_verified"] == len(mine) and verdict["final_blocks_ok"] and verdict["canary_blocks_ok"])
+            ok = (verdict["requests_verified"] == len(mine) and verdict["final_blocks_ok"] and verdict["canary_blocks_ok"]
+                  and verdict["timed_pass_final_blocks_ok"] and verdict["timed_pass_canary_blocks_ok"])
         total_b = sum(r["bytes_transferred"] for r in per_req)
         result = {"rank": rank, "role": "decode", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
-                  "sources": [e.p_rank for e in srcs], "wall_seconds": t_end - t_begin, "bytes_transferred": total_b,
-                  "ingress_GBps": total_b / (t_end - t_begin) / 1e9, "verified": ok, "verification": verdict,
+                  "sources": [e.p_rank for e in srcs], "wall_seconds": wall, "bytes_transferred": total_b,
+                  "ingress_GBps": total_b / wall / 1e9, "verified": ok, "verification": verdict,
                   "requests": per_req}
     else:
         served = _served_by(per_d, me.replica)
@@ -513,38 +534,43 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
         from .control import LeaseTable
 
         leases = LeaseTable(lease_seconds=600.0)
-        for r in served:
-            if cons:
-                leases.grant(f"{r.p_serial}", consumers=len(cons))
-        dist.barrier(group=group)
-        t_begin = time.perf_counter()
-        if gated:
-            # synthetic prefill: each request's layers become ready group by group, prefill_ms per request, one
-            # request after the other on the prefill GPU (a device-side spin stands in for the layer kernels)
-            stream = torch.cuda.current_stream()
-            per_group_cycles = int(cfg.prefill_ms / G * 1e-3 * 1.9e9)  # ~SM clock; only the order of magnitude matters
+        passes = 2 if cfg.verify else 1   # the decode side repeats the stream once more to check every request
+        released = [0] * passes
+        all_released = True
+        for pass_idx in range(passes):
+            base = pass_idx * len(served)
             for r in served:
-                for g in range(G):
-                    if per_group_cycles > 0:
-                        torch.cuda._sleep(per_group_cycles)
-                    for t in cons:  # my position among the prefill ranks decode rank t reads (fan-in when p_tp > d_tp)
-                        feeders = sorted(e.p_rank for e in edges if e.d_rank == t)
-                        w.publish_layers(r.d_rep * 1000 + t, r.p_serial, g, G, stream, src=feeders.index(me.tp_rank),
-                                         n_src=len(feeders))
-        # the producer side only learns of completion through release flags written by the consumers
-        deadline = time.time() + 600
-        pending = {(r.p_serial, ci) for r in served for ci in range(len(cons))}
-        released = 0
-        while pending and time.time() < deadline:
-            for key in sorted(pending)[:64]:
-                serial, ci = key
-                if w.poll(_release_slot(serial, ci, len(cons), w.num_flags), serial + 1):
-                    pending.discard(key)
-                    if leases.release(f"{serial}"):
-                        released += 1
-            time.sleep(0.001)
+                if cons:
+                    leases.grant(f"{pass_idx}:{r.p_serial}", consumers=len(cons))
+            dist.barrier(group=group)
+            if gated:
+                # synthetic prefill: each request's layers become ready group by group, prefill_ms per request, one
+                # request after the other on the prefill GPU (a device-side spin stands in for the layer kernels)
+                stream = torch.cuda.current_stream()
+                per_group_cycles = int(cfg.prefill_ms / G * 1e-3 * 1.9e9)  # ~SM clock; only the order of magnitude matters
+                for r in served:
+                    for g in range(G):
+                        if per_group_cycles > 0:
+                            torch.cuda._sleep(per_group_cycles)
+                        for t in cons:  # my position among the prefill ranks decode rank t reads (fan-in when p_tp > d_tp)
+                            feeders = sorted(e.p_rank for e in edges if e.d_rank == t)
+                            w.publish_layers(r.d_rep * 1000 + t, r.p_serial, g, G, stream, src=feeders.index(me.tp_rank),
+                                             n_src=len(feeders), value=base + r.p_serial + 1)
+            # the producer side only learns of completion through release flags written by the consumers
+            deadline = time.time() + 600
+            pending = {(r.p_serial, ci) for r in served for ci in range(len(cons))}
+            while pending and time.time() < deadline:
+                for key in sorted(pending)[:64]:
+                    serial, ci = key
+                    if w.poll(_release_slot(serial, ci, len(cons), w.num_flags), base + serial + 1):
+                        pending.discard(key)
+                        if leases.release(f"{pass_idx}:{serial}"):
+                            released[pass_idx] += 1
+                time.sleep(0.001)
+            all_released = all_released and not pending
         result = {"rank": rank, "role": "prefill", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
-                  "released": not pending and len(leases) == 0, "requests_served": len(served), "requests_released": released,
+                  "released": all_released and len(leases) == 0, "requests_served": len(served), "requests_released": released[0],
+                  "requests_released_in_verification_pass": released[-1] if passes > 1 else None,
                   "consumers_per_request": len(cons)}
     gathered = [None] * world
     dist.all_gather_object(gathered, result, group=group)
@@ -592,7 +618,8 @@ def summarize(ranks: List[Dict], topo_desc: Dict, cfg: StreamConfig, world: int,
         "time_to_first_token_added_ms": {"p50": pct(ttft, 0.5), "p90": pct(ttft, 0.9), "max": ttft[-1],
                                          "mean": sum(ttft) / len(ttft)},
         "num_descriptors": sum(q["num_descriptors"] for q in reqs),
-        "verified_bit_exact": verified, "verification": "every request when it lands + the whole decode pool at the end" if cfg.verify else "off (verify=0)",
+        "verified_bit_exact": verified, "verification": ("timed pass: the whole decode pool at the end; verification pass (same stream again into a canary-filled pool): "
+                                                            "every request when it lands + the whole pool at the end") if cfg.verify else "off (verify=0)",
         "requests_verified": sum(v["requests_verified"] for v in ver) if ver else 0,
         "blocks_checked": sum(v["final_blocks_checked"] for v in ver) if ver else 0,
         "canary_blocks_checked": sum(v["canary_blocks_checked"] for v in ver) if ver else 0,

@@ -157,6 +157,8 @@ class _Worker:
             self.ctx.handoff_fused(src_pool, src_ids, dst_pool, dst_ids, n, xf, flag, value, stream)
 
     def close(self) -> None:
+        for q in self.__dict__.get("_queues", {}).values():
+            q.stop()
         for views in self.__dict__.get("_slice_cache", {}).values():
             for v in views:
                 v.release()
@@ -214,6 +216,23 @@ class DecodeWorker(_Worker):
         r, l = align_tables(np.asarray(remote_ids, np.int32), np.asarray(local_ids, np.int32))
         self._move(src, r, dst, l, len(l), xf, flag, value, True, h_done, stream)
 
+    def pull_queue(self, key: int, *, edge: Optional[TPEdge] = None, max_ctas: int = 0, idle_us: int = 0):
+        """The resident receiver for prefill worker `key` (kvx_queue_start): requests submitted with pull_queued
+        are served by one persistent kernel, back to back, without a launch per request."""
+        cache = self.__dict__.setdefault("_queues", {})
+        if key not in cache:
+            xf = edge.xform(self.layout) if edge else None
+            cache[key] = self.ctx.queue(self.remotes[key].pool, self.pool, xf, max_ctas=max_ctas, idle_us=idle_us)
+        return cache[key]
+
+    def pull_queued(self, key: int, remote_ids, local_ids, *, notify_slot: Optional[int] = None, value: int = 1,
+                    h_done=None) -> int:
+        """pull() through the resident receiver; returns the ticket (Queue.wait / Queue.poll)."""
+        rem = self.remotes[key]
+        r, l = align_tables(np.asarray(remote_ids, np.int32), np.asarray(local_ids, np.int32))
+        flag = rem.flag_addr(notify_slot) if notify_slot is not None else None
+        return self.pull_queue(key).submit(np.ascontiguousarray(r), np.ascontiguousarray(l), len(l), flag, value, h_done)
+
     def pull_many(self, key: int, requests, *, edge: Optional[TPEdge] = None, stream=None) -> None:
         """All the requests a scheduler step has to receive from one prefill worker, in one launch
         (= the loop over reqs_to_recv in vllm v1/nixl/worker.py:1933-1968).  `requests` is a sequence of
@@ -235,13 +254,14 @@ class PrefillWorker(_Worker):
 
     role = "prefill"
 
-    def publish_layers(self, key: int, seq: int, group: int, groups: int, stream=None, *, src: int = 0, n_src: int = 1) -> None:
+    def publish_layers(self, key: int, seq: int, group: int, groups: int, stream=None, *, src: int = 0, n_src: int = 1,
+                       value: Optional[int] = None) -> None:
         """Layer-wise handoff, producing side: everything queued on `stream` so far has written layer group
         `group` of request `seq` — tell decode worker `key` (an 8-byte store into ITS flag memory, ordered on the
         stream behind the prefill kernels), which lets its pull_layers(…, seq=seq) go."""
         rem = self.remotes[key]
         slot = self.layer_ready_slot(seq, group, groups, rem.meta.num_flags, src, n_src)
-        self.ctx.flag_reset(rem.flag_addr(slot), seq + 1, stream)
+        self.ctx.flag_reset(rem.flag_addr(slot), seq + 1 if value is None else value, stream)
 
     def push(self, key: int, src_ids, dst_ids, *, slot: int, value: int, edge: Optional[TPEdge] = None,
              host_tables: bool = True, h_done=None, stream=None) -> None:

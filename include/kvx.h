@@ -296,6 +296,48 @@ int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, const int32
                            const kvx_pool_desc* dst, const int32_t* h_dst_table, uint32_t n,
                            const kvx_xform* xf, uint64_t* flag, uint64_t flag_val, void* stream);
 
+/*
+ * kvx_queue_* — the resident receiver: the fused handoff of one P→D edge as a persistent kernel fed from a queue,
+ * instead of one launch per request.  It has no counterpart in the transfer agent of the reference's images
+ * (there a request is a descriptor list posted to the transport, [vllm] worker.py:2220-2230); it serves the same
+ * call site — a decode worker receiving request after request from one prefill worker (vllm/disagg.yaml:18-37)
+ * — when prompts are short and the launch, pipeline fill and completion round trip of a per-request kernel
+ * dominate (ISL 1k: ~45 us per request against ~36 us of bytes on one GPU).
+ *
+ * kvx_queue_start binds a queue to (src pool, dst pool, xform): one edge, one geometry.  kvx_queue_submit hands
+ * over a request — host block-id lists (copied and range-checked before the call returns), an optional flag in
+ * device / peer memory and an optional completion word in PINNED host memory, both receiving flag_val once every
+ * byte of THAT request has landed — and returns a ticket; it never launches anything while the kernel is
+ * resident (cost: a few hundred nanoseconds plus the copy of the ids).  Requests are served in order; the CTAs
+ * run from one request into the next without draining their pipelines.  kvx_queue_wait / kvx_queue_poll follow a
+ * ticket from the host; to order GPU work behind a request use its `flag` with kvx_flag_wait on your stream.
+ *
+ * The kernel is resident, not immortal: after `idle_us` (0 = 1000) without a request it parks (exits), and the
+ * next submit launches it again (one ordinary launch latency).  A resident kernel blocks cudaDeviceSynchronize,
+ * cudaFree and everything else that waits for the whole device until it has parked; kvx_queue_park makes it leave
+ * at once (after the submitted requests have landed).  The kernel occupies `max_ctas` CTAs (0 = the context's
+ * geometry for this kind of transfer: every SM on one GPU, ~43 CTAs for a pull over NVLink), all of which must
+ * be co-resident; it runs on a stream of its own, so it is NOT ordered with the caller's streams: the source
+ * blocks must be complete when a request is submitted.  Both pools must use the same block size.  Up to 256
+ * requests can be in flight (submit waits for a free slot, KVX_ETIMEOUT after 10 s); n <= KVX_QUEUE_MAX_BLOCKS.
+ * A queue is used by one host thread at a time; kvx_ctx_destroy stops the context's queues.
+ */
+typedef struct kvx_queue kvx_queue;
+#define KVX_QUEUE_MAX_BLOCKS (1u << 17)
+int32_t kvx_queue_start(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, const kvx_xform* xf,
+                        uint32_t max_ctas, uint32_t idle_us, kvx_queue** out);
+int32_t kvx_queue_submit(kvx_queue* q, const int32_t* h_src_table, const int32_t* h_dst_table, uint32_t n,
+                         uint64_t* flag, uint64_t flag_val, uint64_t* h_done, uint64_t* ticket);
+/* Host-side wait (bounded; KVX_ETIMEOUT) / check (KVX_ENOTREADY) for the request with this ticket. */
+int32_t kvx_queue_wait(kvx_queue* q, uint64_t ticket, uint32_t timeout_ms);
+int32_t kvx_queue_poll(kvx_queue* q, uint64_t ticket);
+/* Wait for everything submitted, then make the kernel leave the GPU now (the next submit brings it back). */
+int32_t kvx_queue_park(kvx_queue* q);
+/* Kernel launches this queue has made so far (1 per resident period) and the CTAs it occupies. */
+int32_t kvx_queue_launch_count(const kvx_queue* q, uint64_t* launches, uint32_t* ctas);
+/* Drain, park and free. */
+int32_t kvx_queue_stop(kvx_queue* q);
+
 #ifdef __cplusplus
 }
 #endif
