@@ -112,6 +112,7 @@ struct kvx_pool {
   std::vector<void*> base;
   std::vector<void*> imported_ptrs;  // to unmap on release
   unsigned long long* d_bases = nullptr;
+  mutable void* d_tmaps = nullptr;  // tensor maps of an NHD pool's regions (built on first use by the tensor-map engine)
   uint64_t chunk_bytes = 0;
   bool local = true;  // the pool's memory lives on the context's own GPU (whoever allocated or exported it)
 };
@@ -256,6 +257,7 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   const uint64_t* notify = nullptr;
   uint32_t notify_count = 0;
   bool block_major = false;  // visit items block by block (cross-layer pools)
+  const kvx_pool* dst_pool = nullptr;  // paged destination as a pool (tensor-map engine)
 };
 
 // int32 entries of the parameter table area a launch needs: both sides' ids, then the notifications
@@ -399,6 +401,64 @@ Geometry resolve_geometry(const kvx_ctx* ctx, bool remote, bool pull, int engine
   return g;
 }
 
+// ---- tensor maps ----------------------------------------------------------------------------------
+// One CUtensorMap per region of an NHD pool: the region as a 4-d tensor (row elements, heads, tokens of a block,
+// blocks) with the pool's own strides; the box is one head's rows of one block — (row, 1, N, 1) — so that a
+// shared-memory slab [N][row] (a head of an HND chunk) lands as N rows, heads*row apart.
+typedef CUresult (*PFN_tensorMapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                             const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                             CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int32_t pool_tensor_maps(kvx_ctx* ctx, const kvx_pool* pool, const void** out) {
+  if (pool->d_tmaps) {
+    *out = pool->d_tmaps;
+    return KVX_OK;
+  }
+  static PFN_tensorMapEncodeTiled encode = nullptr;
+  if (!encode) {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    KVX_CUDA(ctx, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q));
+    if (!f || q != cudaDriverEntryPointSuccess) return KVX_EUNSUPPORTED;
+    encode = reinterpret_cast<PFN_tensorMapEncodeTiled>(f);
+  }
+  const kvx_pool_desc& d = pool->desc;
+  if (d.layout != KVX_LAYOUT_NHD) return KVX_EUNSUPPORTED;
+  const uint64_t row = static_cast<uint64_t>(d.head_dim) * d.elem_bytes;
+  // element type: the widest integer that divides a row and keeps the row within 256 box elements
+  uint32_t es = 0;
+  CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  if (row % 8 == 0 && row / 8 <= 256) { es = 8; dt = CU_TENSOR_MAP_DATA_TYPE_UINT64; }
+  else if (row % 4 == 0 && row / 4 <= 256) { es = 4; dt = CU_TENSOR_MAP_DATA_TYPE_UINT32; }
+  else if (row % 2 == 0 && row / 2 <= 256) { es = 2; dt = CU_TENSOR_MAP_DATA_TYPE_UINT16; }
+  else if (row <= 256) { es = 1; }
+  if (es == 0 || d.block_tokens > 256 || (row * d.block_tokens) % 128 != 0) return KVX_EUNSUPPORTED;
+  std::vector<CUtensorMap> maps(pool->base.size());
+  const cuuint64_t dims[4] = {row / es, d.heads, d.block_tokens, d.num_blocks};
+  const cuuint64_t strides[3] = {row, row * d.heads, d.block_stride};  // bytes, dimensions 1..3
+  const cuuint32_t box[4] = {static_cast<cuuint32_t>(row / es), 1u, d.block_tokens, 1u};
+  const cuuint32_t estr[4] = {1u, 1u, 1u, 1u};
+  for (size_t r = 0; r < pool->base.size(); ++r) {
+    CUresult cr = encode(&maps[r], dt, 4, pool->base[r], dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) {
+      ctx->last_error = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(cr));
+      return KVX_EUNSUPPORTED;
+    }
+  }
+  static_assert(sizeof(CUtensorMap) == 128, "kernels index the map array in 128-byte steps");
+  void* dev = nullptr;
+  KVX_CUDA(ctx, cudaMalloc(&dev, maps.size() * sizeof(CUtensorMap)));
+  cudaError_t e = cudaMemcpy(dev, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(dev);
+    return cuda_fail(ctx, e, "tensor map upload");
+  }
+  pool->d_tmaps = dev;
+  *out = dev;
+  return KVX_OK;
+}
+
 // The default kernel with the request's block ids copied into its parameter block: no H2D copy, no
 // copy-engine hand-over before the launch.
 template <int NT>
@@ -530,6 +590,28 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   if (engine == kEngineTma) {
     // store_mode 0 = thread stores: they match or beat bulk stores at these stage sizes (profiles/r01_sweep_*)
     const size_t smem = static_cast<size_t>(stages) * stage_bytes;
+    // store_mode 3 = tensor-map stores, where the case allows it: HND chunks into an NHD paged pool of the same block
+    // size (the fused handoff's transform and the TP slot); everything else falls through to thread stores
+    const bool tmap_case = store_mode == 3 && !ls.copy_mode && ls.dst_pool != nullptr && ls.h_src_tab == nullptr &&
+                           ls.sg.layout == KVX_LAYOUT_HND && ls.dg.layout == KVX_LAYOUT_NHD && p.src.ratio == 1 && p.dst.ratio == 1 &&
+                           ls.notify_count == 0;
+    if (tmap_case) {
+      const void* maps = nullptr;
+      int32_t rc = pool_tensor_maps(ctx, ls.dst_pool, &maps);
+      if (rc == KVX_OK) {
+        p.dst_tmaps = maps;
+        p.tm_head_bytes = ls.N * ls.R;
+        p.tm_head0 = ls.dg.off;
+        auto k = kvx::kvx_xfer_tmap_kernel;
+        rc = set_smem(ctx, k, smem);
+        if (rc) return rc;
+        KVX_CUDA(ctx, launch_kernel(k, grid, 64u, smem, stream, pdl, p));
+        KVX_CUDA(ctx, cudaGetLastError());
+        ctx->launches++;
+        return KVX_OK;
+      }
+      if (rc != KVX_EUNSUPPORTED) return rc;
+    }
     if (store_mode == 2) {
       if (stages < 2) return KVX_EINVAL;
       auto k = kvx::kvx_xfer_tma_kernel<0, 1>;
@@ -833,6 +915,7 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.flag_val = flag_val;
   ls.flag2 = flag2;
   ls.block_major = regions_inside_one_block(*src) || regions_inside_one_block(*dst);
+  ls.dst_pool = dst;
   ls.dst_is_peer = !dst->local;
   ls.dst_is_peer_known = ls.dst_is_peer;
   ls.src_is_peer = !src->local;
@@ -946,7 +1029,7 @@ int32_t kvx_ctx_set_option(kvx_ctx* ctx, int32_t option, int64_t value) try {
     case KVX_OPT_STAGES: if (value < 0 || value > kvx::kMaxStages) return KVX_EINVAL; break;
     case KVX_OPT_STAGE_BYTES: if (value != 0 && (value < 1024 || value > 200 * 1024 || value % 1024)) return KVX_EINVAL; break;
     case KVX_OPT_CTAS_PER_SM: if (value < 0 || value > 32) return KVX_EINVAL; break;
-    case KVX_OPT_STORE_MODE: if (value < 0 || value > 2) return KVX_EINVAL; break;
+    case KVX_OPT_STORE_MODE: if (value < 0 || value > 3) return KVX_EINVAL; break;
     case KVX_OPT_VEC_BYTES: if (value != 0 && value != 16 && value != 32) return KVX_EINVAL; break;
     case KVX_OPT_CONSUMER_WARPS: if (value < 0 || value > 16) return KVX_EINVAL; break;
     case KVX_OPT_L2_HINT: if (value < 0 || value > 1) return KVX_EINVAL; break;
@@ -1076,6 +1159,7 @@ int32_t kvx_pool_release(kvx_pool* pool) try {
   DeviceGuard guard(pool->ctx->device);
   for (void* p : pool->imported_ptrs) unmap_ptr(pool->ctx, p);
   cudaFree(pool->d_bases);
+  if (pool->d_tmaps) cudaFree(pool->d_tmaps);
   (void)cudaGetLastError();
   delete pool;
   return KVX_OK;

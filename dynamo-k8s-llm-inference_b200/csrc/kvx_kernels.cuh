@@ -65,6 +65,11 @@ struct XferParams {
   unsigned int notify_count, notify_off;
   unsigned int* done_counter;  // scratch: CTAs finished (zero on entry, zero again on exit)
   unsigned int* status;        // scratch: sticky error bits
+  // Tensor-map engine (kvx_xfer_tmap_kernel): one CUtensorMap per destination region over [block][N][H][row],
+  // the permutation HND → NHD done by the TMA unit: one box store per head of a piece.
+  const void* dst_tmaps;       // device array [regions] of CUtensorMap (128 bytes each), or null
+  unsigned int tm_head_bytes;  // bytes of one head's slab in the shared-memory image: N * row
+  unsigned int tm_head0;       // first destination head of piece 0 (TP slot); piece k starts at tm_head0 + k * heads per piece
 };
 
 // ----------------------------------------------------------------------------------------------
@@ -139,6 +144,14 @@ __device__ __forceinline__ void bulk_s2g(unsigned long long gdst, const void* sm
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// TMA tensor store shared → global through a 4-d tensor map (coordinates innermost first): the box's rows leave
+// shared memory densely packed and land wherever the map's strides put them.
+__device__ __forceinline__ void tensor_s2g_4d(const void* tmap, const void* smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<unsigned long long>(tmap)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 template <int N>
 __device__ __forceinline__ void bulk_wait_read() {
   asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
@@ -509,6 +522,111 @@ struct XferParamsTab {
 template <int STORE, int KMAX, int NT>
 __global__ void kvx_xfer_tma_ptab_kernel(const __grid_constant__ XferParamsTab<NT> pt) {
   xfer_tma_body<STORE, KMAX>(pt.p, TabParam{pt.tab});
+}
+
+// ----------------------------------------------------------------------------------------------
+// Tensor-map engine (HND source → NHD paged destination).  Two warps per CTA: the producer of the TMA engine, and
+// one warp that hands every landed piece to the TMA unit again — one cp.async.bulk.tensor store per head, the box
+// (row, 1 head, N tokens, 1 block) of the destination region's tensor map.  No thread touches the payload.
+// ----------------------------------------------------------------------------------------------
+template <class Tab>
+__device__ __forceinline__ void xfer_tmap_body(const XferParams& p, const Tab tab) {
+  extern __shared__ __align__(1024) unsigned char stage_mem[];
+  __shared__ __align__(8) unsigned long long full_bar[kMaxStages];
+  __shared__ __align__(8) unsigned long long empty_bar[kMaxStages];
+  __shared__ int meta_blk[kMaxStages];
+  __shared__ unsigned int meta_reg[kMaxStages], meta_head[kMaxStages], meta_bytes[kMaxStages];
+
+  const unsigned tid = threadIdx.x;
+  const unsigned lane = tid & 31u;
+  const unsigned warp = tid >> 5;
+  const unsigned S = p.stages;
+  grid_dep_launch_dependents();
+  if (tid == 0) {
+    for (unsigned s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1u);
+      mbar_init(&empty_bar[s], 1u);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const unsigned bid = blockIdx.x;
+  const unsigned grid = gridDim.x;
+  const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+  const unsigned heads_per_piece = p.piece_bytes / p.tm_head_bytes;
+
+  if (warp == 0) {
+    grid_dep_wait();
+    RawItem raw{};
+    if (lane < my_items) item_load(p, tab, bid + lane * grid, raw);
+    unsigned s = 0, phase = 0;
+    for (unsigned base = 0; base < my_items; base += 32u) {
+      unsigned long long sa = 0, da = 0;
+      unsigned bytes = 0;
+      if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
+      const int my_blk = raw.d.id;
+      const unsigned my_reg = raw.r, my_piece = raw.piece;
+      if (base + 32u + lane < my_items) item_load(p, tab, bid + (base + 32u + lane) * grid, raw);
+      const unsigned cnt = min(32u, my_items - base);
+      for (unsigned j = 0; j < cnt; ++j) {
+        const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
+        const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
+        const int blk = __shfl_sync(0xffffffffu, my_blk, j);
+        const unsigned reg = __shfl_sync(0xffffffffu, my_reg, j);
+        const unsigned piece = __shfl_sync(0xffffffffu, my_piece, j);
+        mbar_wait(&empty_bar[s], phase ^ 1u);
+        unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+        if (lane == 0) {
+          meta_blk[s] = blk;
+          meta_reg[s] = reg;
+          meta_head[s] = p.tm_head0 + piece * heads_per_piece;
+          meta_bytes[s] = nbytes;
+          mbar_arrive_expect_tx(&full_bar[s], nbytes);
+        }
+        __syncwarp();
+        if (nbytes != 0) {
+          if (p.s_runs == 1u) {
+            if (lane == 0) bulk_g2s(stage, src, nbytes, &full_bar[s]);
+          } else {
+            for (unsigned x = lane; x < p.s_runs; x += 32u)
+              bulk_g2s(stage + x * p.s_run_bytes, src + static_cast<unsigned long long>(x) * p.s_stride, p.s_run_bytes,
+                       &full_bar[s]);
+          }
+        }
+        if (++s == S) { s = 0; phase ^= 1u; }
+      }
+    }
+  } else {
+    // a stage is handed back one item late, so that two items' stores stay in flight
+    unsigned prev_stage = 0;
+    bool have_prev = false;
+    grid_dep_wait();
+    unsigned s = 0, phase = 0;
+    for (unsigned it = 0; it < my_items; ++it) {
+      mbar_wait(&full_bar[s], phase);
+      const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+      if (meta_bytes[s] != 0) {
+        const unsigned char* tm = static_cast<const unsigned char*>(p.dst_tmaps) + static_cast<size_t>(meta_reg[s]) * 128u;
+        for (unsigned h = lane; h < heads_per_piece; h += 32u)
+          tensor_s2g_4d(tm, stage + static_cast<size_t>(h) * p.tm_head_bytes, 0, static_cast<int>(meta_head[s] + h), 0, meta_blk[s]);
+      }
+      bulk_commit();
+      if (have_prev) {
+        bulk_wait_read<1>();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[prev_stage]);
+      }
+      prev_stage = s;
+      have_prev = true;
+      if (++s == S) { s = 0; phase ^= 1u; }
+    }
+    bulk_wait<0>();  // every byte written before the completion fence
+  }
+  finish_and_flag(p, tab);
+}
+
+__global__ void __launch_bounds__(64) kvx_xfer_tmap_kernel(const __grid_constant__ XferParams p) {
+  xfer_tmap_body(p, TabGlobal{});
 }
 
 // ----------------------------------------------------------------------------------------------

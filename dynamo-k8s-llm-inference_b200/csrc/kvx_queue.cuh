@@ -36,13 +36,22 @@ struct QueueDesc {  // one request as published to the CTAs (device memory)
   unsigned long long seq1;                  // seq + 1 (what the per-slot host completion word receives)
 };
 
-struct QueueHostSlot {  // one request as submitted by the host (pinned host memory, 64 bytes)
-  unsigned long long seq1;  // seq + 1 of the request in this slot; written LAST by the host
-  unsigned int n, tab_off;  // blocks; first entry of [src ids n][dst ids n] in the table rings
-  unsigned long long flag, flag_val, done;
-  unsigned long long pad[3];
+// One request as submitted by the host (pinned host memory, one 64-byte line): four 16-byte chunks, each a
+// payload word and a tag = queue_tag(seq + 1) ^ payload.  The dispatcher reads a slot with one 16-byte load per
+// chunk — eight slots per poll, one PCIe round trip for "is it there" AND "what is it" — and takes a chunk only
+// when its tag fits the sequence number it expects, so a chunk caught half-written, or left from the request that
+// used the slot a ring lap ago, is never mistaken for the new one, whatever the granularity of the reads.
+struct QueueHostSlot {
+  unsigned long long n_tab, tag0;   // n | tab_off << 32: blocks; first entry of [src ids n][dst ids n] in the table rings
+  unsigned long long flag, tag1;
+  unsigned long long flag_val, tag2;
+  unsigned long long done, tag3;
 };
 static_assert(sizeof(QueueHostSlot) == 64, "one slot = one 64-byte line");
+__host__ __device__ __forceinline__ unsigned long long queue_tag(unsigned long long seq1) {
+  return seq1 * 0x9E3779B97F4A7C15ull;  // odd multiplier: non-zero for every seq1 >= 1, so zeroed memory never validates
+}
+constexpr unsigned kQueuePollSlots = 8;  // slots looked at per poll (4 lanes each)
 
 struct QueueParams {
   XferParams x;                  // the edge's geometry (plan, strides, region bases); n, total_items, tables per request
@@ -98,39 +107,51 @@ struct TabQueue {
 __device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned lane) {
   unsigned long long seq = q.start[q.gen & 1u];
   unsigned long long t_idle = global_timer_ns();
+  const unsigned grp = lane >> 2, chunk = lane & 3u;
+  auto poll = [&](unsigned long long at, unsigned long long& payload) -> unsigned {
+    // lanes 4g..4g+3 read the four chunks of slot at+g; returns how many consecutive slots from `at` hold their request
+    const unsigned long long* c = reinterpret_cast<const unsigned long long*>(q.h_slots + ((at + grp) & q.ring_mask)) + 2u * chunk;
+    unsigned long long tag;
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0,%1}, [%2];" : "=l"(payload), "=l"(tag) : "l"(c) : "memory");
+    const unsigned ok = __ballot_sync(0xffffffffu, tag == (queue_tag(at + grp + 1) ^ payload));
+    unsigned k = 0;
+    while (k < kQueuePollSlots && ((ok >> (4u * k)) & 0xfu) == 0xfu) ++k;
+    return k;
+  };
   for (;;) {
-    const QueueHostSlot* hs = q.h_slots + (seq & q.ring_mask);
-    unsigned long long have = 0;
-    if (lane == 0) have = ld_acquire_sys(&hs->seq1);
-    have = __shfl_sync(0xffffffffu, have, 0);
-    if (have == seq + 1) {
-      // the slot's other fields were written before seq1 (host release) and are read after it (acquire)
-      unsigned n = 0, tab_off = 0;
-      unsigned long long flag = 0, val = 0, done = 0;
-      if (lane == 0) {
-        const volatile QueueHostSlot* v = hs;
-        n = v->n; tab_off = v->tab_off; flag = v->flag; val = v->flag_val; done = v->done;
+    unsigned long long payload = 0;
+    const unsigned k = poll(seq, payload);
+    if (k != 0) {
+      // every group's fields, gathered into all of its lanes
+      const unsigned g0 = lane & ~3u;
+      const unsigned long long n_tab = __shfl_sync(0xffffffffu, payload, g0);
+      const unsigned long long flag = __shfl_sync(0xffffffffu, payload, g0 + 1u);
+      const unsigned long long val = __shfl_sync(0xffffffffu, payload, g0 + 2u);
+      const unsigned long long done = __shfl_sync(0xffffffffu, payload, g0 + 3u);
+      // id lists of the k requests, [src n][dst n] padded to 16 bytes by the host: host ring → device ring, same offset;
+      // the reads of all requests are in flight together
+      for (unsigned r = 0; r < k; ++r) {
+        const unsigned long long nt = __shfl_sync(0xffffffffu, n_tab, 4u * r);
+        const unsigned n = static_cast<unsigned>(nt), tab_off = static_cast<unsigned>(nt >> 32);
+        const unsigned quads = (2u * n + 3u) / 4u;
+        const int4* src = reinterpret_cast<const int4*>(q.h_tables + tab_off);
+        int4* dst = reinterpret_cast<int4*>(q.tables + tab_off);
+        for (unsigned i = lane; i < quads; i += 32u) {
+          int4 v;
+          asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i) : "memory");
+          dst[i] = v;
+        }
       }
-      n = __shfl_sync(0xffffffffu, n, 0);
-      tab_off = __shfl_sync(0xffffffffu, tab_off, 0);
-      // both id lists, [src n][dst n], padded to 16 bytes by the host: host ring → device ring, same offset
-      const unsigned quads = (2u * n + 3u) / 4u;
-      const int4* src = reinterpret_cast<const int4*>(q.h_tables + tab_off);
-      int4* dst = reinterpret_cast<int4*>(q.tables + tab_off);
-      for (unsigned i = lane; i < quads; i += 32u) {
-        int4 v;
-        asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i));
-        dst[i] = v;
+      if (chunk == 0 && grp < k) {
+        QueueDesc* d = q.desc + ((seq + grp) & q.ring_mask);
+        const unsigned n = static_cast<unsigned>(n_tab);
+        d->n = n; d->tab_off = static_cast<unsigned>(n_tab >> 32); d->total_items = n * q.items_per_block;
+        d->flag = flag; d->flag_val = val; d->done = done; d->seq1 = seq + grp + 1;
       }
-      if (lane == 0) {
-        QueueDesc* d = q.desc + (seq & q.ring_mask);
-        d->n = n; d->tab_off = tab_off; d->total_items = n * q.items_per_block;
-        d->flag = flag; d->flag_val = val; d->done = done; d->seq1 = seq + 1;
-      }
-      __threadfence();  // every lane's table stores and lane 0's descriptor, before the publication
+      __threadfence();  // every lane's table and descriptor stores, before the publication
       __syncwarp();
-      if (lane == 0) st_release_gpu(q.pub_seq, seq + 1);
-      ++seq;
+      seq += k;
+      if (lane == 0) st_release_gpu(q.pub_seq, seq);
       t_idle = global_timer_ns();
       continue;
     }
@@ -138,14 +159,13 @@ __device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned la
     if (lane == 0) stop = *reinterpret_cast<const volatile unsigned int*>(q.h_stop);
     stop = __shfl_sync(0xffffffffu, stop, 0);
     if (stop != 0 || global_timer_ns() - t_idle > q.idle_ns) {
-      unsigned long long again = 0;
       if (lane == 0) {
         st_release_sys(q.h_parked, seq + 1);
         __threadfence_system();
-        again = ld_acquire_sys(&hs->seq1);
       }
-      again = __shfl_sync(0xffffffffu, again, 0);
-      if (again == seq + 1 && stop == 0) {  // a request slipped in between the last look and the announcement
+      __syncwarp();
+      const unsigned again = poll(seq, payload);
+      if (again != 0 && stop == 0) {  // a request slipped in between the last look and the announcement
         t_idle = global_timer_ns();
         continue;
       }
@@ -156,7 +176,7 @@ __device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned la
       }
       return;
     }
-    __nanosleep(200);
+    __nanosleep(100);
   }
 }
 

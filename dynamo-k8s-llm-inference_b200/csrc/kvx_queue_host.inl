@@ -254,11 +254,16 @@ int32_t kvx_queue_submit(kvx_queue* q, const int32_t* h_src_table, const int32_t
     q->spans.push_back(QueueSpan{seq + 1, b, e});
   }
   q->tab_cursor = e;
-  kvx::QueueHostSlot* hs = q->slots + (seq & (kQueueRing - 1));
-  hs->n = n; hs->tab_off = b;
-  hs->flag = reinterpret_cast<uint64_t>(flag); hs->flag_val = flag_val; hs->done = done_dev;
+  // the ids first, then the slot: each 16-byte chunk carries its payload and a tag that only fits this sequence number
   std::atomic_thread_fence(std::memory_order_release);
-  *const_cast<volatile unsigned long long*>(&hs->seq1) = seq + 1;
+  volatile kvx::QueueHostSlot* hs = q->slots + (seq & (kQueueRing - 1));
+  const unsigned long long tag = kvx::queue_tag(seq + 1);
+  const unsigned long long w0 = static_cast<unsigned long long>(n) | (static_cast<unsigned long long>(b) << 32);
+  const unsigned long long w1 = reinterpret_cast<uint64_t>(flag), w2 = flag_val, w3 = done_dev;
+  hs->n_tab = w0; hs->tag0 = tag ^ w0;
+  hs->flag = w1; hs->tag1 = tag ^ w1;
+  hs->flag_val = w2; hs->tag2 = tag ^ w2;
+  hs->done = w3; hs->tag3 = tag ^ w3;
   q->seq = seq + 1;
   if (ticket) *ticket = seq + 1;
   // mirror image of the kernel's parking: slot first, full fence, then look whether a kernel is there to see it

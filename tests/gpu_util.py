@@ -38,6 +38,8 @@ ENGINE_CONFIGS = [
     dict(engine="tma", store_mode=2, stages=6, stage_bytes=32768, consumer_warps=8, ctas_per_sm=2, l2_hint=1),
     dict(engine="tma", max_ctas=5, pdl=0),          # bounded SM footprint, plain launches
     dict(engine="tma", stages=6, stage_bytes=32768, ctas_per_sm=1, max_ctas=43),   # the geometry NVLink transfers default to
+    dict(engine="tma", store_mode=3),                                     # tensor-map stores where the case allows, else thread stores
+    dict(engine="tma", store_mode=3, stages=6, stage_bytes=32768, ctas_per_sm=3),
 ]
 
 
