@@ -592,9 +592,14 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     const size_t smem = static_cast<size_t>(stages) * stage_bytes;
     // store_mode 3 = tensor-map stores, where the case allows it: HND chunks into an NHD paged pool of the same block
     // size (the fused handoff's transform and the TP slot); everything else falls through to thread stores
-    const bool tmap_case = store_mode == 3 && !ls.copy_mode && ls.dst_pool != nullptr && ls.h_src_tab == nullptr &&
-                           ls.sg.layout == KVX_LAYOUT_HND && ls.dg.layout == KVX_LAYOUT_NHD && p.src.ratio == 1 && p.dst.ratio == 1 &&
-                           ls.notify_count == 0;
+    // store_mode 0 picks them by itself where they measured faster: 8 KiB pieces of two or more heads on one GPU (chunks
+    // of TP4 shards of an 8-head model: 6.30 against 5.95 TB/s, tools/tmap_variants.py), two CTAs per SM
+    const bool tmap_shape = !ls.copy_mode && ls.dst_pool != nullptr && ls.h_src_tab == nullptr && ls.sg.layout == KVX_LAYOUT_HND &&
+                            ls.dg.layout == KVX_LAYOUT_NHD && p.src.ratio == 1 && p.dst.ratio == 1 && ls.notify_count == 0;
+    const bool tmap_auto = store_mode == 0 && tmap_shape && !remote && pl.piece_bytes == 8192u && ls.N * ls.R <= 4096u &&
+                           ctx->opt[KVX_OPT_STAGES] == 0 && ctx->opt[KVX_OPT_STAGE_BYTES] == 0 && ctx->opt[KVX_OPT_CONSUMER_WARPS] == 0 &&
+                           ctx->opt[KVX_OPT_VEC_BYTES] == 0;
+    const bool tmap_case = (store_mode == 3 && tmap_shape) || tmap_auto;
     if (tmap_case) {
       const void* maps = nullptr;
       int32_t rc = pool_tensor_maps(ctx, ls.dst_pool, &maps);
@@ -605,7 +610,10 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
         auto k = kvx::kvx_xfer_tmap_kernel;
         rc = set_smem(ctx, k, smem);
         if (rc) return rc;
-        KVX_CUDA(ctx, launch_kernel(k, grid, 64u, smem, stream, pdl, p));
+        uint32_t tgrid = grid;
+        if (tmap_auto && ctx->opt[KVX_OPT_CTAS_PER_SM] == 0 && ctx->opt[KVX_OPT_MAX_CTAS] == 0)
+          tgrid = std::min<uint32_t>(static_cast<uint32_t>(ctx->sms) * 2u, p.total_items);
+        KVX_CUDA(ctx, launch_kernel(k, tgrid, 64u, smem, stream, pdl, p));
         KVX_CUDA(ctx, cudaGetLastError());
         ctx->launches++;
         return KVX_OK;

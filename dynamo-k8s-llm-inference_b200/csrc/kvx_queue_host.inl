@@ -276,6 +276,16 @@ int32_t kvx_queue_submit(kvx_queue* q, const int32_t* h_src_table, const int32_t
   return KVX_OK;
 } KVX_CATCH_ALL
 
+int32_t kvx_queue_submit_batch(kvx_queue* q, const kvx_batch_item* items, uint32_t count, uint64_t* last_ticket) try {
+  if (!q || (count != 0 && !items)) return KVX_EINVAL;
+  for (uint32_t k = 0; k < count; ++k) {
+    const kvx_batch_item& it = items[k];
+    int32_t rc = kvx_queue_submit(q, it.h_src_table, it.h_dst_table, it.n, it.flag, it.flag_val, it.h_done, last_ticket);
+    if (rc) return rc;  // requests before k are queued and will be served
+  }
+  return KVX_OK;
+} KVX_CATCH_ALL
+
 int32_t kvx_queue_wait(kvx_queue* q, uint64_t ticket, uint32_t timeout_ms) try {
   if (!q || ticket == 0 || ticket > q->seq) return KVX_EINVAL;
   if (ticket + kQueueRing <= q->seq) return KVX_OK;  // its slot has long been handed on: it had landed by then

@@ -75,6 +75,7 @@ PROTOTYPES = {
     "kvx_handoff_batch": (c_i32, [c_vp, c_vp, c_vp, P(BatchItem), c_u32, P(XformC), c_vp]),
     "kvx_queue_start": (c_i32, [c_vp, c_vp, c_vp, P(XformC), c_u32, c_u32, P(c_vp)]),
     "kvx_queue_submit": (c_i32, [c_vp, c_vp, c_vp, c_u32, c_vp, c_u64, c_vp, P(c_u64)]),
+    "kvx_queue_submit_batch": (c_i32, [c_vp, P(BatchItem), c_u32, P(c_u64)]),
     "kvx_queue_wait": (c_i32, [c_vp, c_u64, c_u32]),
     "kvx_queue_poll": (c_i32, [c_vp, c_u64]),
     "kvx_queue_park": (c_i32, [c_vp]),

@@ -308,6 +308,30 @@ class Queue:
                                                       _ptr(h_done), ctypes.byref(t)), "kvx_queue_submit")
         return t.value
 
+    @staticmethod
+    def pack(requests):
+        """A scheduler step's requests as a kvx_batch_item array for submit_many: a sequence of (h_src_ids, h_dst_ids,
+        flag or None, flag_val, pinned h_done or None).  Returns (array, keepalive)."""
+        import numpy as np
+
+        keep, arr = [], (BatchItem * len(requests))()
+        for k, (s_ids, d_ids, flag, val, h_done) in enumerate(requests):
+            n = 0 if d_ids is None else len(d_ids)
+            if n:
+                s_ids = np.ascontiguousarray(s_ids, dtype=np.int32)
+                d_ids = np.ascontiguousarray(d_ids, dtype=np.int32)
+                keep += [s_ids, d_ids]
+            arr[k] = BatchItem(_ptr(s_ids) if n else None, _ptr(d_ids) if n else None, n, 0, flag, int(val), _ptr(h_done))
+        return arr, keep
+
+    def submit_many(self, packed, count: Optional[int] = None) -> int:
+        """kvx_queue_submit_batch: all requests of a step with one call; returns the LAST ticket."""
+        arr = packed[0] if isinstance(packed, tuple) else packed
+        t = c_u64()
+        self.ctx._check(self.ctx.lib.kvx_queue_submit_batch(self.handle, arr, len(arr) if count is None else count, ctypes.byref(t)),
+                        "kvx_queue_submit_batch")
+        return t.value
+
     def wait(self, ticket: int, timeout_ms: int = 5000) -> None:
         self.ctx._check(self.ctx.lib.kvx_queue_wait(self.handle, ticket, timeout_ms), "kvx_queue_wait")
 

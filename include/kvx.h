@@ -331,6 +331,10 @@ int32_t kvx_queue_start(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, 
                         uint32_t max_ctas, uint32_t idle_us, kvx_queue** out);
 int32_t kvx_queue_submit(kvx_queue* q, const int32_t* h_src_table, const int32_t* h_dst_table, uint32_t n,
                          uint64_t* flag, uint64_t flag_val, uint64_t* h_done, uint64_t* ticket);
+/* Every request of a scheduler step in one call (the items of kvx_handoff_batch: lists, flag, value, pinned word
+ * per request).  Unlike kvx_handoff_batch each request is complete, and notified, on its own; *last_ticket is the
+ * ticket of the last one (tickets are consecutive).  On an error the requests before the failing one stay queued. */
+int32_t kvx_queue_submit_batch(kvx_queue* q, const kvx_batch_item* items, uint32_t count, uint64_t* last_ticket);
 /* Host-side wait (bounded; KVX_ETIMEOUT) / check (KVX_ENOTREADY) for the request with this ticket. */
 int32_t kvx_queue_wait(kvx_queue* q, uint64_t ticket, uint32_t timeout_ms);
 int32_t kvx_queue_poll(kvx_queue* q, uint64_t ticket);

@@ -119,6 +119,35 @@ def test_queue_ring_and_table_ring_wrap():
     c.close()
 
 
+def test_queue_scheduler_step_in_one_call():
+    """kvx_queue_submit_batch: a step's requests with one call, each with its own flag and completion word."""
+    c = kvx.Context(0)
+    nb = 300
+    src = o.make_pool(2, 8, 128, nb, o.HND, seed=8)
+    dst = o.make_pool(2, 8, 128, nb, o.NHD, fill="canary")
+    ds, dd = DevPool(c, src), DevPool(c, dst)
+    flags, _ = c.flags()
+    words = torch.zeros(12, dtype=torch.int64).pin_memory()
+    perm_s, perm_d = o.make_table(nb, 240, 1), o.make_table(nb, 240, 2)
+    reqs, at = [], 0
+    for k, n in enumerate([8, 40, 0, 3, 64, 16, 1, 30, 8, 8, 50, 12]):
+        reqs.append((perm_s[at:at + n] if n else None, perm_d[at:at + n] if n else None, flags + 8 * (40 + k), 7 + k, words[k:k + 1]))
+        at += n
+    with c.queue(ds.kp, dd.kp) as q:
+        last = q.submit_many(q.pack(reqs))
+        for t in range(last - 11, last + 1):   # tickets of one call are consecutive
+            q.wait(t)
+        assert words.tolist() == [7 + k for k in range(12)]
+        q.park()
+    for s_ids, d_ids, *_ in reqs:
+        if d_ids is not None:
+            o.handoff(src, s_ids, dst, d_ids)
+    assert np.array_equal(dd.bytes(), dst.buf)
+    for k in range(12):
+        assert c.flag_poll(flags + 8 * (40 + k), 7 + k)
+    c.close()
+
+
 def test_queue_tp_slice_and_errors():
     c = kvx.Context(0)
     nb = 50
