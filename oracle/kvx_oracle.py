@@ -177,6 +177,23 @@ def _resolve(xf: Optional[Xform], src_heads: Optional[int], dst_heads: Optional[
     return so, do, hc, sl
 
 
+def touched(pool: Pool, table: Sequence[int], head_off: int = 0, heads: Optional[int] = None) -> List[tuple]:
+    """The byte ranges (offset into pool.buf, length) one side of a transfer touches, region-major then in table
+    order: descriptor (region r, block id b) = region base + b * block stride ([vllm] v1/nixl/worker.py:113-115 for the
+    id, :1108-1133 for the address, blocks-first K/V as two virtual regions), and for a head slice of an HND chunk the
+    `heads` heads from `head_off` on, which are contiguous: + head_off * N * row, heads * N * row long ([vllm]
+    worker.py:1159-1168 on the remote side, :152-192 on the local side)."""
+    if pool.layout != HND and (head_off != 0 or (heads is not None and heads != pool.heads)):
+        raise ValueError("a head slice is one contiguous range only in HND chunks")
+    heads = pool.heads if heads is None else heads
+    head_bytes = pool.block_tokens * pool.row_bytes
+    out = []
+    for r in range(pool.regions):
+        for b in table:
+            out.append((pool.region_off[r] + int(b) * pool.block_stride + head_off * head_bytes, heads * head_bytes))
+    return out
+
+
 def _check_table(table: np.ndarray, num_blocks: int) -> np.ndarray:
     t = np.asarray(table, dtype=np.int64)
     if t.size and (t.min() < 0 or t.max() >= num_blocks):

@@ -205,7 +205,8 @@ def addressing_fixture():
                        "local_per_source": [[[int(a) - BASE, int(n_)] for a, n_, _ in h] for h in handles]}
                 out["hetero_tp"].append(row)
     # --- prefix-cache hits on the decode side: which remote blocks are read
-    for n_remote, n_local in ((9, 9), (9, 4), (9, 1), (9, 0), (1, 1)):
+    # (an empty local list never reaches this helper: a full prefix hit only notifies, worker.py:2166-2185)
+    for n_remote, n_local in ((9, 9), (9, 4), (9, 1), (17, 16), (1, 1)):
         ns = types.SimpleNamespace(_has_mamba=False)
         remote_ids = (1 + rng.permutation(40)[:n_remote]).tolist()
         local_ids = (1 + rng.permutation(40)[:n_local]).tolist()

@@ -212,6 +212,47 @@ def test_golden_fixture_on_gpu(cfg_ctx, golden_dir):
     assert np.array_equal(ddst.bytes(), np.ascontiguousarray(g["d_expect"]).view(np.uint8).reshape(-1))
 
 
+def test_golden_addressing_fixture_on_gpu(ctx, golden_dir):
+    """The kernel against the connector's own byte ranges (tests/golden/addressing.json, generated from [vllm]
+    _build_fa_remote / _build_local_splits_from_plan): for every heterogeneous-TP row, each edge must copy exactly
+    remote range -> local range for the request's blocks and nothing else.  The oracle is not involved."""
+    import json
+
+    from kvx.tp import plan_edges
+
+    rows = json.load(open(os.path.join(golden_dir, "addressing.json")))["hetero_tp"]
+    rng = np.random.Generator(np.random.PCG64(99))
+    for row in rows:
+        H, N, D, E, L = row["total_kv_heads"], row["block_tokens"], row["head_dim"], row["elem_bytes"], row["layers"]
+        arr = "blocks_first" if row["blocks_first"] else "split"
+        hp, hd = H // row["p_tp"], H // row["d_tp"]
+        edges = [e for e in plan_edges(row["p_tp"], row["d_tp"], H) if e.d_rank == row["d_rank"]]
+        dst = o.make_pool(L, hd, D, row["nb_d"], o.HND, block_tokens=N, elem_bytes=E, arrangement=arr, fill="canary")
+        want = dst.buf.copy()
+        ddst = DevPool(ctx, dst)
+        n = 4
+        for k, e in enumerate(edges):
+            src = o.make_pool(L, hp, D, row["nb_p"], o.HND, block_tokens=N, elem_bytes=E, arrangement=arr, seed=100 + e.p_rank)
+            dsrc = DevPool(ctx, src)
+            ts = (1 + rng.permutation(row["nb_p"] - 1)[:n]).astype(np.int32)
+            td = (1 + rng.permutation(row["nb_d"] - 1)[:n]).astype(np.int32)   # every edge of the request writes the same blocks
+            if k:
+                td = td_first
+            td_first = td
+            ctx.handoff_fused(dsrc.kp, dev_table(ts), ddst.kp, dev_table(td), n, kvx.Xform(e.src_head_off, e.dst_head_off, e.heads, kvx.HND))
+            torch.cuda.synchronize()
+            for r in range(2 * L):
+                for i in range(n):
+                    so, sl = row["remote"][r * row["nb_p"] + int(ts[i])]
+                    do_, dl = row["local_per_source"][k][r * row["nb_d"] + int(td[i])]
+                    assert sl == dl
+                    want[do_:do_ + dl] = src.buf[so:so + sl]
+            dsrc.kp.release()
+        assert np.array_equal(ddst.bytes(), want), row
+        ddst.kp.release()
+    ctx.check()
+
+
 def test_empty_and_single(ctx):
     src = o.make_pool(1, 8, 64, 4, o.NHD, seed=1)
     dst = o.make_pool(1, 8, 64, 4, o.HND, fill="canary")

@@ -295,3 +295,73 @@ def test_baseline_config1_exact_size_numpy_vs_c():
         untouched = np.ones(nb, dtype=bool)
         untouched[td] = False
         assert (want.region_view(0)[untouched].view(np.uint16) == o.CANARY16).all()
+
+
+# ---- addressing pinned to the on-box connector's own descriptor code (tests/golden/addressing.json) ----------------
+def _addressing(golden_dir):
+    import json
+
+    with open(os.path.join(golden_dir, "addressing.json")) as f:
+        return json.load(f)
+
+
+def _geom_pool(L, H, D, nb, N, E, arrangement):
+    """A pool record with the fixture's geometry and no contents (only offsets matter here)."""
+    p = o.make_pool(L, H, D, 2, o.HND, block_tokens=N, elem_bytes=E, arrangement=arrangement, fill="canary")
+    chunk = N * H * D * E
+    if arrangement == "split":
+        p.region_off = [r * nb * chunk for r in range(2 * L)]
+    else:
+        p.region_off = [l * nb * 2 * chunk + kv * chunk for l in range(L) for kv in range(2)]
+    p.num_blocks = nb
+    return p
+
+
+def test_golden_descriptor_addressing(golden_dir):
+    """Which bytes a request touches in a pool: descriptor ids and addresses as [vllm] _compute_desc_ids and
+    _build_fa_local produce them, split K/V pools and blocks-first joint pools (K and V as two virtual regions)."""
+    for row in _addressing(golden_dir)["local"]:
+        pool = _geom_pool(row["layers"], row["heads"], row["head_dim"], row["num_blocks"], row["block_tokens"], row["elem_bytes"],
+                          row["arrangement"])
+        ids = row["block_ids"]
+        assert row["desc_ids"] == [r * row["num_blocks"] + b for r in range(pool.regions) for b in ids]
+        assert [list(t) for t in o.touched(pool, ids)] == row["touched"], row["arrangement"]
+
+
+def test_golden_heterogeneous_tp_byte_offsets(golden_dir):
+    """Heterogeneous TP in bytes: what a decode rank reads inside every prefill block ([vllm] _build_fa_remote) and where
+    each source rank's heads land inside its own blocks (_build_local_splits_from_plan) — against the oracle's head
+    slices driven by the product's edge planner (kvx/tp.py)."""
+    from kvx.tp import plan_edges
+
+    rows = _addressing(golden_dir)["hetero_tp"]
+    assert len(rows) == 28
+    for row in rows:
+        H, N, D, E, L = row["total_kv_heads"], row["block_tokens"], row["head_dim"], row["elem_bytes"], row["layers"]
+        arr = "blocks_first" if row["blocks_first"] else "split"
+        hp, hd = H // row["p_tp"], H // row["d_tp"]
+        P = _geom_pool(L, hp, D, row["nb_p"], N, E, arr)
+        Dp = _geom_pool(L, hd, D, row["nb_d"], N, E, arr)
+        edges = [e for e in plan_edges(row["p_tp"], row["d_tp"], H) if e.d_rank == row["d_rank"]]
+        assert [e.p_rank for e in edges] == row["source_ranks"]
+        for k, e in enumerate(edges):
+            # every prefill rank of the request has the same geometry: one remote list serves them all
+            assert [list(t) for t in o.touched(P, range(row["nb_p"]), e.src_head_off, e.heads)] == row["remote"], row
+            assert [list(t) for t in o.touched(Dp, range(row["nb_d"]), e.dst_head_off, e.heads)] == row["local_per_source"][k], row
+
+
+def test_golden_prefix_hit_alignment(golden_dir):
+    """Prefix-cache hit on the decode side: the LAST len(local) remote blocks are read ([vllm] _apply_prefix_caching) —
+    the product's align_tables and the oracle's handoff must pick the same ones."""
+    from kvx.workers import align_tables
+
+    for row in _addressing(golden_dir)["prefix"]:
+        s, d = align_tables(np.array(row["remote"], np.int32), np.array(row["local"], np.int32))
+        assert s.tolist() == row["remote_read"] and d.tolist() == row["local_written"]
+        src = o.make_pool(1, 2, 8, 42, o.NHD, seed=1)
+        dst = o.make_pool(1, 2, 8, 42, o.NHD, fill="canary")
+        want = o.make_pool(1, 2, 8, 42, o.NHD, fill="canary")
+        o.handoff(src, row["remote"], dst, row["local"])
+        if row["local"]:
+            o.handoff(src, row["remote_read"], want, row["local_written"])
+        assert np.array_equal(dst.buf, want.buf)

@@ -71,6 +71,8 @@ CONFIGS = (
     ("tiny_everywhere_3x8k_x2", dict(stages=3, stage_bytes=8192, ctas_per_sm=2, max_ctas=296, consumer_warps=4)),
     ("small_4x8k_x1", dict(stages=4, stage_bytes=8192, ctas_per_sm=1, max_ctas=148, consumer_warps=4)),
 )
+if os.environ.get("CORUN_SET") == "max_ctas":   # the SM footprint of the pull as the caller bounds it (KVX_OPT_MAX_CTAS)
+    CONFIGS = tuple((f"max_ctas_{k}", dict(stages=6, stage_bytes=32768, ctas_per_sm=1, max_ctas=k)) for k in (16, 24, 43, 148))
 for name, opts in CONFIGS:
     for k in ("stages", "stage_bytes", "ctas_per_sm", "max_ctas"):
         dctx.set_option(k, opts.get(k, 0))
