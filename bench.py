@@ -563,7 +563,7 @@ def brief(summary, extra=()):
     keys = ("requests", "concurrency", "route", "aggregate_throughput_GBps", "per_request_throughput_GBps_median",
             "per_edge_throughput_GBps_median", "per_decode_rank_ingress_GBps", "pct_of_nvlink_900", "per_isl",
             "time_to_first_token_added_ms", "xfer_time_seconds", "verified_bit_exact", "requests_verified",
-            "blocks_checked", "canary_blocks_checked", "prefill_blocks_released", "releases_observed", "wall_seconds") + tuple(extra)
+            "blocks_checked", "canary_blocks_checked", "verification_failures", "prefill_blocks_released", "releases_observed", "wall_seconds") + tuple(extra)
     out = {k: summary[k] for k in keys if k in summary}
     for k, v in list(out.items()):
         if isinstance(v, float):
@@ -689,6 +689,64 @@ def run_pairs(args):
     w.ctx.check()
     if rank == 0:
         clocks = sampler.stop()
+
+    # Short requests (ISL 1k, 128 MiB): per-request cost over NVLink is the bytes plus ~20 us of launch and link round
+    # trips.  Per request through the per-request entry (launch) and through the resident receiver (kvx_queue_*), one at
+    # a time ("single": submit -> completion observed, then the next) and back to back ("stream"); host wall clock on
+    # the decode rank, all pairs at once.  Same (source, destination) block pairs as the headline's sets, so the
+    # whole-pool verification below covers what these moved.
+    short = None
+    if not args.no_extras and pull:
+        m_short = shape.blocks_for(1024)
+        R = 16
+        rec = {}
+        if not is_p:
+            ids = [(np.ascontiguousarray(perm_p[j * m_short:(j + 1) * m_short]), np.ascontiguousarray(perm_d[j * m_short:(j + 1) * m_short])) for j in range(R)]
+            word = torch.zeros(1, dtype=torch.int64).pin_memory()
+            q = w.pull_queue(0)
+
+            def q_single():
+                for a_, b_ in ids:
+                    q.wait(q.submit(a_, b_, m_short), 10000)
+
+            def q_stream():
+                for a_, b_ in ids:
+                    t_ = q.submit(a_, b_, m_short)
+                q.wait(t_, 10000)
+
+            def l_single():
+                for a_, b_ in ids:
+                    w.pull(0, a_, b_, host_tables=True, h_done=word, stream=stream)
+                    stream.synchronize()
+
+            def l_stream():
+                for a_, b_ in ids:
+                    w.pull(0, a_, b_, host_tables=True, stream=stream)
+                stream.synchronize()
+
+            b_short = m_short * shape.regions * shape.chunk_bytes()
+            for name, fn in (("queue_single", q_single), ("queue_stream", q_stream), ("launch_single", l_single), ("launch_stream", l_stream)):
+                if name == "launch_single":
+                    q.park()
+                fn(); fn()
+                best = 1e9
+                for _ in range(5):
+                    t0 = time.perf_counter()
+                    fn()
+                    best = min(best, time.perf_counter() - t0)
+                rec[name + "_us"] = round(1e6 * best / R, 2)
+                rec[name + "_GBps"] = round(b_short / (best / R) / 1e9, 1)
+            rec["queue_ctas"] = q.ctas
+            q.park()
+            torch.cuda.synchronize()
+        allr = [None] * world
+        dist.all_gather_object(allr, rec)
+        if rank == 0:
+            dec = [r for r in allr if r]
+            short = {"isl": 1024, "payload_MiB_each": round(m_short * shape.regions * shape.chunk_bytes() / 2**20, 1), "requests": R,
+                     "per_request_min_over_pairs": {k: (min if k.endswith("GBps") else max)(r[k] for r in dec) for k in dec[0]},
+                     "note": "worst pair; queue_single = one request at a time through the resident receiver (concurrency 1)"}
+        dist.barrier()
 
     # pair 0 alone (the other pairs idle): what the concurrent pairs cost each other
     active = rank in (0, pairs)
@@ -916,7 +974,7 @@ def run_pairs(args):
             "verified_bit_exact": verified, "blocks_checked": int(vstat[1]), "canary_blocks_checked": int(vstat[2]),
             "verification": "every decode rank: ENTIRE pool (all regions of every block, block 0 included) against the expected pool "
                             "rebuilt from the prefill rank's seed, after the timed, e2e, one-pair and staged runs",
-            "staged_path": staged, "baselines": baselines, **legs,
+            "short_requests_isl1k": short, "staged_path": staged, "baselines": baselines, **legs,
         }
         os.write(json_fd, (json.dumps(line) + "\n").encode())
     os.close(json_fd)

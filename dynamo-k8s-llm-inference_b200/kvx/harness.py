@@ -208,6 +208,7 @@ class _Verifier:
             self.src[key] = t.view(shape.regions, nb, words_p)
             self.src_layout[key] = p_layouts[key]
         self.ok = torch.ones(1, dtype=torch.int32, device=f"cuda:{me.device}")
+        self.stream.wait_stream(torch.cuda.current_stream())  # the regenerated source was written on the current stream
         self.per_req: List[object] = []
         self.canary = np.array(0xC0DE, dtype=np.uint16).view(np.int16).item()
 
@@ -624,6 +625,10 @@ def summarize(ranks: List[Dict], topo_desc: Dict, cfg: StreamConfig, world: int,
         "blocks_checked": sum(v["final_blocks_checked"] for v in ver) if ver else 0,
         "canary_blocks_checked": sum(v["canary_blocks_checked"] for v in ver) if ver else 0,
         "verification_source_bytes": sorted({s for v in ver for s in v["source_bytes"]}),
+        "verification_failures": [{"replica": r["replica"], "tp_rank": r["tp_rank"],
+                                   **{k: r["verification"][k] for k in ("requests_verified", "requests_checked", "first_bad_request", "final_blocks_ok",
+                                                                        "canary_blocks_ok", "timed_pass_final_blocks_ok", "timed_pass_canary_blocks_ok")}}
+                                  for r in dec if r.get("verification") and r["verified"] is not True],
         "prefill_blocks_released": all(r["released"] for r in pre),
         "releases_observed": sum(r["requests_released"] for r in pre), "releases_expected": sum(r["requests_served"] for r in pre if r["consumers_per_request"]),
         "seed": SEED,
