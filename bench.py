@@ -538,12 +538,12 @@ def pull_ncu_traffic():
         return None, None
 
 
-def harness_leg(dist, rank, world, topo, cfg, group_ranks=None):
+def harness_leg(dist, rank, world, topo, cfg, group_ranks=None, n_devices=None):
     """One verified request stream through kvx.harness.run_rank on the ranks torchrun started (the same code
     `run-benchmarks.sh -u kvx://...` runs in processes of its own).  Ranks outside `group_ranks` sit it out."""
     from kvx import harness
 
-    plans = harness.rank_plans(topo, world)
+    plans = harness.rank_plans(topo, n_devices or world)
     group = None
     if group_ranks is not None and len(group_ranks) != world:
         group = dist.new_group(ranks=group_ranks, backend="gloo")  # collective: every rank creates it
@@ -572,10 +572,24 @@ def brief(summary, extra=()):
     return out
 
 
+def phase(name):
+    """Progress marker on stderr (every rank): which part of a multi-GPU run a hang or a failure belongs to."""
+    sys.stderr.write(f"[bench rank {os.environ.get('RANK', '0')} +{time.perf_counter() - _T0:7.2f}s] {name}\n")
+    sys.stderr.flush()
+
+
+_T0 = time.perf_counter()
+
+
 def run_pairs(args):
+    import faulthandler
+
     import numpy as np
     import torch
     import torch.distributed as dist
+
+    # a multi-GPU run that stops making progress dumps every thread's stack and exits instead of hanging the box
+    faulthandler.dump_traceback_later(int(os.environ.get("KVX_BENCH_TIMEOUT", "900")), exit=True)
 
     import kvx
     from kvx import harness, synth
@@ -585,13 +599,28 @@ def run_pairs(args):
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
     assert world == args.gpus and world % 2 == 0, "pairs need an even number of ranks"
+    one_gpu = args.one_gpu   # debugging aid: every rank on cuda:0 (a one-GPU box can walk through the N-rank logic)
+    if one_gpu:
+        local = 0
     torch.cuda.set_device(local)
     # stdout carries exactly one JSON line: everything native libraries print there (NCCL's version
     # banner) is sent to stderr by pointing fd 1 at fd 2 for the whole run; the line goes to the saved fd.
     sys.stdout.flush()
     json_fd = os.dup(1)
     os.dup2(2, 1)
-    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{local}"))
+    if one_gpu:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+    else:
+        dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=torch.device(f"cuda:{local}"))
+
+    def all_reduce(t, op):
+        if one_gpu:   # gloo reduces host tensors
+            h = t.cpu()
+            dist.all_reduce(h, op=op)
+            t.copy_(h)
+        else:
+            dist.all_reduce(t, op=op)
+
     hbm_peak, peak_src = load_peaks()
     shape = kvx.KV_SHAPES["meta-llama/Llama-3.1-8B"]
     isl = args.isl
@@ -655,6 +684,7 @@ def run_pairs(args):
 
     torch.cuda.synchronize()
     dist.barrier()
+    phase("headline: warm-up + timed steps")
     for k in range(args.warmup):
         step(k)
     torch.cuda.synchronize()
@@ -673,6 +703,7 @@ def run_pairs(args):
     w.ctx.check()
 
     # e2e through the host-table entry on the moving side; the other side waits on its flag
+    phase("e2e steps")
     base = 100000
     done = torch.zeros(total_steps, dtype=torch.int64).pin_memory()
     torch.cuda.synchronize()
@@ -696,6 +727,7 @@ def run_pairs(args):
     # the decode rank, all pairs at once.  Same (source, destination) block pairs as the headline's sets, so the
     # whole-pool verification below covers what these moved.
     short = None
+    phase("short requests (queue / launch)")
     if not args.no_extras and pull:
         m_short = shape.blocks_for(1024)
         R = 16
@@ -750,6 +782,7 @@ def run_pairs(args):
 
     # pair 0 alone (the other pairs idle): what the concurrent pairs cost each other
     active = rank in (0, pairs)
+    phase("pair 0 alone")
     torch.cuda.synchronize()
     dist.barrier()
     ms_alone = timed_loop(torch, stream, lambda k: step(k, slot=3, base=0, active=active), alone_steps) if active else 0.0
@@ -762,6 +795,7 @@ def run_pairs(args):
     # and the CPU-staged handoff (D2H of the request's blocks into pinned host memory -> host
     # memcpy-per-row transform -> H2D -> scatter)
     staged, baselines = None, None
+    phase("staged path + library / CPU-staged baselines")
     threads = len(os.sched_getaffinity(0))
     if not args.no_extras:
         reps = 5
@@ -879,6 +913,7 @@ def run_pairs(args):
     # Bit-exactness of EVERYTHING that landed: the decode rank regenerates its prefill peer's pool from the seed
     # (same generator, on this GPU — not through the mapping the transfer used), builds the expected decode pool
     # for every block set the run touched, and compares the ENTIRE pool: touched blocks, canary blocks, block 0.
+    phase("whole-pool verification")
     vstat = torch.zeros(3, dtype=torch.int64, device="cuda")  # [ok, touched blocks, canary blocks]
     if not is_p:
         canary = np.array(synth.CANARY16, dtype=np.uint16).view(np.int16).item()
@@ -896,13 +931,15 @@ def run_pairs(args):
         vstat[2] = nb - len(used_sets) * n
         del src, exp
     ok = vstat[:1].clone() if not is_p else torch.ones(1, dtype=torch.int64, device="cuda")
-    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-    dist.all_reduce(vstat[1:], op=dist.ReduceOp.SUM)
+    all_reduce(ok, dist.ReduceOp.MIN)
+    vsum = vstat[1:].clone()
+    all_reduce(vsum, dist.ReduceOp.SUM)
+    vstat[1:] = vsum
 
     t = torch.tensor([ms, e2e_s * 1e3, ms_alone], device="cuda", dtype=torch.float64)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    all_reduce(t, dist.ReduceOp.MAX)
     lt = torch.tensor([float(launches)], device="cuda", dtype=torch.float64)
-    dist.all_reduce(lt, op=dist.ReduceOp.SUM)
+    all_reduce(lt, dist.ReduceOp.SUM)
     ms_max, e2e_ms, alone_ms = float(t[0]), float(t[1]), float(t[2])
     dist.barrier()
     w.close()
@@ -910,6 +947,7 @@ def run_pairs(args):
 
     # CPU baseline of the same request (host pools, the C restatement on every host thread), rank 0, bounded
     cpu = None
+    phase("cpu baseline (rank 0)")
     if rank == 0 and not args.no_extras:
         cpu_gbps, cpu_reps, _, _ = cpu_handoff_rate(shape, isl, min_seconds=6.0, max_reps=100, threads=threads)
         cpu = {"value": round(cpu_gbps, 3), "unit": UNIT, "cores": threads, "kind": "port",
@@ -921,24 +959,32 @@ def run_pairs(args):
     legs = {}
     if not args.no_extras:
         M8, M70 = "meta-llama/Llama-3.1-8B", "meta-llama/Llama-3.1-70B"
+        ndev = 1 if one_gpu else world
         topo = synthetic_topology(pairs, pairs, 1, 1, "vllm", M8, decode_layout=kvx.NHD)
-        for c in (1, 4):  # config #3's load shape: 64-request closed loop at ISL 8192 per pair, concurrency 1 and 4
+        want = [x for x in args.legs.split(",") if x]
+        for c in ((1, 4) if ("all" in want or "config3" in want) else ()):  # config #3's load shape: 64-request closed loop at ISL 8192 per pair, concurrency 1 and 4
+            phase(f"leg config3 c={c}")
             cfg = harness.StreamConfig(model=M8, isl=[8192] * args.stream_requests, concurrency=c)
-            legs[f"config3_stream_isl8k_c{c}"] = brief(harness_leg(dist, rank, world, topo, cfg))
+            legs[f"config3_stream_isl8k_c{c}"] = brief(harness_leg(dist, rank, world, topo, cfg, n_devices=ndev))
         # config #5's: every pair its own stream of 32 requests, ISL log-uniform over 1k..32k, all pairs at once
-        choices = [1024, 2048, 4096, 8192, 16384, 32768]
+        choices = [1024, 2048, 4096, 8192] if one_gpu else [1024, 2048, 4096, 8192, 16384, 32768]
         per_rep = [harness.draw_isls(args.mixed_requests, choices, 5 + 17 * d) for d in range(pairs)]
-        cfg = harness.StreamConfig(model=M8, isl=per_rep[0], per_replica_isl=per_rep, concurrency=1)
-        legs["config5_mixed_isl"] = brief(harness_leg(dist, rank, world, topo, cfg))
+        if "all" in want or "config5" in want:
+            phase("leg config5 mixed ISL")
+            cfg = harness.StreamConfig(model=M8, isl=per_rep[0], per_replica_isl=per_rep, concurrency=1)
+            legs["config5_mixed_isl"] = brief(harness_leg(dist, rank, world, topo, cfg, n_devices=ndev))
         # config #4's: TP reshard on transfer, prefill TP = 2 x decode TP, every edge concurrent.  6 of 8 GPUs run
         # TP4 -> TP2 (Llama-3.1-70B); with 4 GPUs the same code runs TP2 -> TP1 on 3 of them.
-        if world >= 4:
+        if world >= 4 and ("all" in want or "config4" in want):
             ptp, dtp = (4, 2) if world >= 6 else (2, 1)
+            phase(f"leg config4 TP{ptp}->TP{dtp}")
             topo4 = synthetic_topology(1, 1, ptp, dtp, "vllm", M70)
             cfg = harness.StreamConfig(model=M70, isl=[8192] * 8, concurrency=1)
-            s4 = harness_leg(dist, rank, world, topo4, cfg, group_ranks=list(range(ptp + dtp)))
+            s4 = harness_leg(dist, rank, world, topo4, cfg, group_ranks=list(range(ptp + dtp)), n_devices=ndev)
             legs[f"config4_tp{ptp}_to_tp{dtp}"] = brief(s4)
 
+    phase("done")
+    faulthandler.cancel_dump_traceback_later()
     if rank == 0:
         ms_step = ms_max / args.steps
         per_pair = payload / (ms_step / 1e3) / 1e9
@@ -998,6 +1044,9 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="N=1: skip the per-kernel table, ISL sweep and CPU baseline (profiling runs)")
     ap.add_argument("--stream-requests", type=int, default=64, help="N>1: requests per pair in the config #3 closed-loop streams")
     ap.add_argument("--mixed-requests", type=int, default=32, help="N>1: requests per pair in the config #5 mixed-ISL stream")
+    ap.add_argument("--one-gpu", action="store_true", help="N>1 debugging aid: all ranks share cuda:0 (gloo only; numbers meaningless)")
+    ap.add_argument("--legs", default="all", help="N>1: which verified request-stream legs run after the headline: all | none | "
+                                                  "comma list of config3,config4,config5")
     ap.add_argument("--mode", default="pull", choices=["pull", "push"],
                     help="N>1: decode GPU reads the prefill pool (pull, default) or prefill GPU stores into the decode pool")
     args = ap.parse_args()

@@ -24,6 +24,7 @@ from __future__ import annotations
 import json
 import os
 import socket
+import sys
 import statistics
 import time
 from dataclasses import asdict, dataclass, field
@@ -301,6 +302,8 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
     world = len(plans)
     me = plans[rank]
     shape = KV_SHAPES[cfg.model]
+    trace = (lambda m: (sys.stderr.write(f"[harness rank {rank} {me.role}{me.replica}/tp{me.tp_rank}] {m}\n"), sys.stderr.flush())) \
+        if os.environ.get("KVX_HARNESS_TRACE") else (lambda m: None)
     p_ranks = [p for p in plans if p.role == "prefill"]
     d_ranks = [p for p in plans if p.role == "decode"]
     p_tp, d_tp = p_ranks[0].tp_size, d_ranks[0].tp_size
@@ -322,8 +325,10 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
     else:
         synth.fill_canary(w.kv)
     torch.cuda.synchronize()
+    trace("pool ready, handshake")
     metas = [None] * world
     dist.all_gather_object(metas, w.metadata(), group=group)
+    trace("handshake done")
 
     def p_rank_of(rep: int, t: int) -> int:
         return next(p.rank for p in p_ranks if p.replica == rep and p.tp_rank == t)
@@ -362,6 +367,7 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
             """One run of the whole stream.  `ver` = the verifier that checks every request as it lands (the
             verification pass), or None (the timed pass: nothing but the transfers touches the GPU)."""
             val_of = lambda r: pass_idx * served_on[r.p_rep] + r.p_serial + 1  # noqa: E731
+            trace(f"pass {pass_idx} starts")
             lanes = [[torch.cuda.Stream() for _ in srcs] for _ in range(c)]
             ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in mine]
             ev_ready = [torch.cuda.Event(enable_timing=True) for _ in mine]  # gated streams: last layer group is ready
@@ -543,6 +549,7 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
             for r in served:
                 if cons:
                     leases.grant(f"{pass_idx}:{r.p_serial}", consumers=len(cons))
+            trace(f"pass {pass_idx}: barrier")
             dist.barrier(group=group)
             if gated:
                 # synthetic prefill: each request's layers become ready group by group, prefill_ms per request, one
@@ -569,10 +576,12 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
                             released[pass_idx] += 1
                 time.sleep(0.001)
             all_released = all_released and not pending
+            trace(f"pass {pass_idx}: {released[pass_idx]} of {len(served)} released")
         result = {"rank": rank, "role": "prefill", "replica": me.replica, "tp_rank": me.tp_rank, "device": me.device,
                   "released": all_released and len(leases) == 0, "requests_served": len(served), "requests_released": released[0],
                   "requests_released_in_verification_pass": released[-1] if passes > 1 else None,
                   "consumers_per_request": len(cons)}
+    trace("stream done, gathering results")
     gathered = [None] * world
     dist.all_gather_object(gathered, result, group=group)
     dist.barrier(group=group)
