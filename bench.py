@@ -538,20 +538,17 @@ def pull_ncu_traffic():
         return None, None
 
 
-def harness_leg(dist, rank, world, topo, cfg, group_ranks=None, n_devices=None):
+def harness_leg(dist, rank, world, topo, cfg, n_devices=None):
     """One verified request stream through kvx.harness.run_rank on the ranks torchrun started (the same code
-    `run-benchmarks.sh -u kvx://...` runs in processes of its own).  Ranks outside `group_ranks` sit it out."""
+    `run-benchmarks.sh -u kvx://...` runs in processes of its own).  Ranks the topology does not need only take part
+    in the collectives."""
     from kvx import harness
 
     plans = harness.rank_plans(topo, n_devices or world)
-    group = None
-    if group_ranks is not None and len(group_ranks) != world:
-        group = dist.new_group(ranks=group_ranks, backend="gloo")  # collective: every rank creates it
+    res = harness.run_rank(rank, plans, cfg, world_size=world)
     summary = None
-    if group_ranks is None or rank in group_ranks:
-        res = harness.run_rank(rank, plans, cfg, group=group)
-        if rank == 0:
-            summary = harness.summarize(res["all"], topo.describe(), cfg, len(plans), world)
+    if rank == 0:
+        summary = harness.summarize(res["all"], topo.describe(), cfg, len(plans), n_devices or world)
     dist.barrier()
     return summary
 
@@ -980,7 +977,7 @@ def run_pairs(args):
             phase(f"leg config4 TP{ptp}->TP{dtp}")
             topo4 = synthetic_topology(1, 1, ptp, dtp, "vllm", M70)
             cfg = harness.StreamConfig(model=M70, isl=[8192] * 8, concurrency=1)
-            s4 = harness_leg(dist, rank, world, topo4, cfg, group_ranks=list(range(ptp + dtp)), n_devices=ndev)
+            s4 = harness_leg(dist, rank, world, topo4, cfg, n_devices=ndev)
             legs[f"config4_tp{ptp}_to_tp{dtp}"] = brief(s4)
 
     phase("done")

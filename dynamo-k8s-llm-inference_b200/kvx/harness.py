@@ -289,9 +289,11 @@ class _Verifier:
                 "regions_per_block": self.shape.regions, "source_bytes": sorted(set(self.mode.values()))}
 
 
-def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) -> Optional[Dict]:
+def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, world_size: Optional[int] = None) -> Optional[Dict]:
     """One worker rank's part of the stream.  torch.distributed is initialised (any backend that moves Python
-    objects and barriers on CPU tensors), the rank's device is current.  Returns this rank's result record."""
+    objects and barriers on CPU tensors), the rank's device is current.  Returns this rank's result record.
+    `world_size` > len(plans): the job has more ranks than the topology needs (TP4 -> TP2 uses 6 of 8 GPUs); the extra
+    ranks only take part in the collectives, so no sub-group has to be created."""
     import torch
     import torch.distributed as dist
 
@@ -299,7 +301,14 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None) ->
     from .api import HND, NHD  # noqa: F401
     from .workers import DecodeWorker, PrefillWorker
 
-    world = len(plans)
+    world = world_size or len(plans)
+    if rank >= len(plans):  # spectator: the same collectives in the same order, nothing else
+        dist.all_gather_object([None] * world, None, group=group)
+        for _ in range(2 if cfg.verify else 1):
+            dist.barrier(group=group)
+        dist.all_gather_object([None] * world, None, group=group)
+        dist.barrier(group=group)
+        return None
     me = plans[rank]
     shape = KV_SHAPES[cfg.model]
     trace = (lambda m: (sys.stderr.write(f"[harness rank {rank} {me.role}{me.replica}/tp{me.tp_rank}] {m}\n"), sys.stderr.flush())) \
