@@ -519,6 +519,13 @@ def run_single(args):
                          "sample": f"{cpu_reps} requests of ISL {isl} ({payload / 2**20:.0f} MiB each) between host pools, "
                                    "oracle/kvx_oracle.c memcpy-per-row HND->NHD"},
         "added_ttft_ms_isl8k": round(ms_step, 4) if isl == 8192 else None,
+        # what the fused kernel replaces, timed in this run on the same request: the post-process the reference's images run
+        # on the decode GPU today (land raw blocks, index_select -> permute -> index_copy_ per layer tensor), the CPU-staged
+        # handoff, and the pure-host handoff.  The e2e / cpu_baseline ratio compares HBM-resident data with host-resident
+        # data; the first of these three is the like-for-like one.
+        "same_run_speedups": {"vs_torch_land_then_postprocess": round(baselines["torch_land_then_index_select_permute_index_copy"]["ms"] / ms_step, 1),
+                              "vs_cpu_staged_gpu_handoff": round(baselines["cpu_staged_d2h_hostmemcpy_h2d"]["ms"] / ms_step, 1),
+                              "vs_host_memcpy_handoff": round(value / cpu_gbps, 1)},
         "kernels": parts, "isl_sweep": sweep, "short_requests_host_entry": short, "resident_queue": queue, "tp_shard_chunks": shards, "baselines": baselines,
         "options": {k: ctx.get_option(k) for k in kvx.OPT},
     }

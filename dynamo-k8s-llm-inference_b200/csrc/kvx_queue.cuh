@@ -181,7 +181,7 @@ __device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned la
 }
 
 // A published descriptor, read past L1 (the slot is rewritten while the kernel lives).
-__device__ __forceinline__ QueueDesc load_desc(const QueueDesc* p) {
+__device__ __forceinline__ QueueDesc load_desc_full(const QueueDesc* p) {
   const volatile QueueDesc* v = p;
   QueueDesc d;
   d.n = v->n; d.tab_off = v->tab_off; d.total_items = v->total_items; d.reserved = 0;
@@ -247,7 +247,7 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
         if (block) mbar_wait(&empty_bar[e.stage], e.parity);
         else if (!mbar_try_wait(&empty_bar[e.stage], e.parity)) break;
         if (lane == 0) {
-          const QueueDesc d = load_desc(q.desc + e.slot);
+          const QueueDesc d = load_desc_full(q.desc + e.slot);
           queue_count_done(q, d, e.slot);
         }
         pend_head = (pend_head + 1u) % (kMaxStages + 1u);
@@ -255,46 +255,76 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
       }
     };
     unsigned long long seq = q.start[q.gen & 1u];
+    unsigned long long pub_known = 0;  // requests known to be published (saves the poll when several were published at once)
     unsigned s = 0, phase = 0;
-    for (;;) {
-      // wait for request `seq`, or for the park
-      bool leave = false;
-      for (;;) {
-        unsigned long long pub = 0, pk = 0;
-        if (lane == 0) {
-          pub = ld_acquire_gpu(q.pub_seq);
-          pk = ld_acquire_gpu(q.park);
-        }
-        pub = __shfl_sync(0xffffffffu, pub, 0);
-        pk = __shfl_sync(0xffffffffu, pk, 0);
-        if (pub > seq) break;
-        drain(false);
-        if ((pk >> 40) == q.gen && seq >= (pk & ((1ull << 40) - 1))) { leave = true; break; }
-        __nanosleep(100);
-      }
-      if (leave) break;
-      const unsigned slot = static_cast<unsigned>(seq & q.ring_mask);
-      unsigned dn = 0, dtab = 0, dtotal = 0;
-      if (lane == 0) {
-        const volatile QueueDesc* d = q.desc + slot;
+    XferParams rp = p;                 // the request being served: the edge's geometry + its n, total_items, table offsets
+    const TabQueue tab{q.tables};
+    RawItem raw{};
+    bool primed = false;               // rp and raw already hold request `seq` (set up while the previous request was issued)
+    auto load_desc = [&](unsigned long long at, unsigned& dn, unsigned& dtab, unsigned& dtotal) {
+      if (lane == 0) {                 // issued here, consumed by the caller's shuffles later
+        const volatile QueueDesc* d = q.desc + (at & q.ring_mask);
         dn = d->n; dtab = d->tab_off; dtotal = d->total_items;
       }
+    };
+    auto adopt = [&](unsigned dn, unsigned dtab, unsigned dtotal) {
       dn = __shfl_sync(0xffffffffu, dn, 0);
       dtab = __shfl_sync(0xffffffffu, dtab, 0);
       dtotal = __shfl_sync(0xffffffffu, dtotal, 0);
-      XferParams rp = p;  // this request's view of the edge
       rp.n = dn; rp.total_items = dtotal;
       rp.src.tab_off = dtab; rp.dst.tab_off = dtab + dn;
-      const TabQueue tab{q.tables};
+      const unsigned items = bid < dtotal ? (dtotal - bid + grid - 1u) / grid : 0u;
+      if (lane < items) item_load(rp, tab, bid + lane * grid, raw);
+    };
+    for (;;) {
+      if (!primed) {
+        // wait for request `seq`, or for the park
+        bool leave = false;
+        while (pub_known <= seq) {
+          unsigned long long pub = 0, pk = 0;
+          if (lane == 0) {
+            pub = ld_acquire_gpu(q.pub_seq);
+            pk = ld_acquire_gpu(q.park);
+          }
+          pub_known = __shfl_sync(0xffffffffu, pub, 0);
+          pk = __shfl_sync(0xffffffffu, pk, 0);
+          __syncwarp();  // lane 0's acquire orders the other lanes' table and descriptor loads behind the publication
+          if (pub_known > seq) break;
+          drain(false);
+          if ((pk >> 40) == q.gen && seq >= (pk & ((1ull << 40) - 1))) { leave = true; break; }
+          __nanosleep(100);
+        }
+        if (leave) break;
+        unsigned dn = 0, dtab = 0, dtotal = 0;
+        load_desc(seq, dn, dtab, dtotal);
+        adopt(dn, dtab, dtotal);
+      }
+      primed = false;
+      const unsigned slot = static_cast<unsigned>(seq & q.ring_mask);
+      const unsigned dtotal = rp.total_items;
       const unsigned my_items = bid < dtotal ? (dtotal - bid + grid - 1u) / grid : 0u;
       unsigned last_stage = 0, last_parity = 0;
-      RawItem raw{};
-      if (lane < my_items) item_load(rp, tab, bid + lane * grid, raw);
       for (unsigned base = 0; base < my_items; base += 32u) {
         unsigned long long sa = 0, da = 0;
         unsigned bytes = 0;
         if (base + lane < my_items) item_finish(rp, raw, sa, da, bytes);
-        if (base + 32u + lane < my_items) item_load(rp, tab, bid + (base + 32u + lane) * grid, raw);
+        const bool last_batch = base + 32u >= my_items;
+        unsigned ndn = 0, ndtab = 0, ndtotal = 0;
+        bool next_ready = false;
+        if (!last_batch) {
+          if (base + 32u + lane < my_items) item_load(rp, tab, bid + (base + 32u + lane) * grid, raw);
+        } else {
+          // Last batch of this request: while it is being issued, fetch the next request's descriptor (and below its
+          // first table lookups), so that the ring does not run dry between two requests.
+          if (pub_known <= seq + 1) {
+            unsigned long long pub = 0;
+            if (lane == 0) pub = ld_acquire_gpu(q.pub_seq);
+            pub_known = __shfl_sync(0xffffffffu, pub, 0);
+            __syncwarp();
+          }
+          next_ready = pub_known > seq + 1;
+          if (next_ready) load_desc(seq + 1, ndn, ndtab, ndtotal);
+        }
         const unsigned cnt = min(32u, my_items - base);
         for (unsigned j = 0; j < cnt; ++j) {
           const unsigned long long src = __shfl_sync(0xffffffffu, sa, j);
@@ -321,10 +351,14 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
           last_stage = s; last_parity = phase;
           if (++s == S) { s = 0; phase ^= 1u; }
         }
+        if (next_ready) {  // every use of rp for THIS request lies behind us: make it the next request's
+          adopt(ndn, ndtab, ndtotal);
+          primed = true;
+        }
       }
       if (my_items == 0) {
         if (lane == 0) {  // nothing of this request falls to this CTA: it still counts
-          const QueueDesc d = load_desc(q.desc + slot);
+          const QueueDesc d = load_desc_full(q.desc + slot);
           queue_count_done(q, d, slot);
         }
       } else {
