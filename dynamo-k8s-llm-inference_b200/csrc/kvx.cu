@@ -104,6 +104,7 @@ struct kvx_ctx {
   std::map<void*, Imported> imported;  // pointers handed out by import_record
   std::map<const void*, size_t> smem_limit;  // kernel → dynamic shared memory limit already set
   std::vector<struct kvx_queue*> queues;      // resident receivers started on this context (stopped with it)
+  std::map<void*, uint64_t> vmm_allocs;       // kvx_mem_alloc_vmm ranges
 };
 
 struct kvx_pool {
@@ -113,11 +114,18 @@ struct kvx_pool {
   std::vector<void*> imported_ptrs;  // to unmap on release
   unsigned long long* d_bases = nullptr;
   mutable void* d_tmaps = nullptr;  // tensor maps of an NHD pool's regions (built on first use by the tensor-map engine)
+  struct VmmRange {
+    CUdeviceptr va;
+    uint64_t size;
+  };
+  std::vector<VmmRange> vmm_ranges;  // address ranges mapped by kvx_pool_import_fds (unmapped on release)
   uint64_t chunk_bytes = 0;
   bool local = true;  // the pool's memory lives on the context's own GPU (whoever allocated or exported it)
 };
 
 namespace {
+
+void pool_unmap_vmm(kvx_pool* pool);  // kvx_vmm_host.inl
 
 int32_t cuda_fail(kvx_ctx* ctx, cudaError_t e, const char* what) {
   if (ctx) {
@@ -1021,6 +1029,7 @@ int32_t kvx_ctx_destroy(kvx_ctx* ctx) try {
       cudaFree(ctx->d_flags);
       cudaFree(ctx->d_counters);
       cudaFree(ctx->d_table_ring);
+      while (!ctx->vmm_allocs.empty()) kvx_mem_free_vmm(ctx, ctx->vmm_allocs.begin()->first);
       for (auto& u : ctx->ring_uses) cudaEventDestroy(u.done);
       if (ctx->h_table_ring) cudaFreeHost(ctx->h_table_ring);
       (void)cudaGetLastError();
@@ -1168,6 +1177,10 @@ int32_t kvx_pool_release(kvx_pool* pool) try {
   for (void* p : pool->imported_ptrs) unmap_ptr(pool->ctx, p);
   cudaFree(pool->d_bases);
   if (pool->d_tmaps) cudaFree(pool->d_tmaps);
+  if (!pool->vmm_ranges.empty()) {
+    cudaDeviceSynchronize();
+    pool_unmap_vmm(pool);
+  }
   (void)cudaGetLastError();
   delete pool;
   return KVX_OK;
@@ -1718,3 +1731,4 @@ extern "C" int32_t kvx_handoff_static(int32_t device, const kvx_pool_desc* src, 
 } KVX_CATCH_ALL
 
 #include "kvx_queue_host.inl"
+#include "kvx_vmm_host.inl"

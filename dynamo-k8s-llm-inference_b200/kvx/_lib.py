@@ -62,6 +62,10 @@ PROTOTYPES = {
     "kvx_pool_exportable": (c_i32, [c_vp, P(c_i32)]),
     "kvx_pool_region_base": (c_i32, [c_vp, c_u32, P(c_vp)]),
     "kvx_pool_slice": (c_i32, [c_vp, c_u32, c_u32, P(c_vp)]),
+    "kvx_mem_alloc_vmm": (c_i32, [c_vp, c_u64, c_u64, P(c_vp)]),
+    "kvx_mem_free_vmm": (c_i32, [c_vp, c_vp]),
+    "kvx_pool_export_fds": (c_i32, [c_vp, c_vp, P(c_sz), P(c_i32), P(c_u32)]),
+    "kvx_pool_import_fds": (c_i32, [c_vp, c_vp, c_sz, P(c_i32), c_u32, P(c_vp)]),
     "kvx_ctx_flags": (c_i32, [c_vp, P(c_vp), P(c_u32)]),
     "kvx_flag_reset": (c_i32, [c_vp, c_vp, c_u64, c_vp]),
     "kvx_flag_wait": (c_i32, [c_vp, c_vp, c_u64, c_u32, c_vp]),

@@ -102,6 +102,16 @@ class Pool:
         self.ctx._check(self.ctx.lib.kvx_pool_exportable(self.handle, ctypes.byref(out)), "kvx_pool_exportable")
         return bool(out.value)
 
+    def export_fds(self):
+        """(record, fds) of a pool in VMM memory (kvx_pool_export_fds): send the record and pass the fds with SCM_RIGHTS
+        (socket.send_fds), then close them."""
+        need, cnt = c_sz(0), c_u32(0)
+        self.ctx.lib.kvx_pool_export_fds(self.handle, None, ctypes.byref(need), None, ctypes.byref(cnt))
+        buf = ctypes.create_string_buffer(need.value)
+        fds = (c_i32 * max(1, cnt.value))()
+        self.ctx._check(self.ctx.lib.kvx_pool_export_fds(self.handle, buf, ctypes.byref(need), fds, ctypes.byref(cnt)), "kvx_pool_export_fds")
+        return buf.raw[: need.value], list(fds[: cnt.value])
+
     def release(self) -> None:
         if self.handle:
             self.ctx.lib.kvx_pool_release(self.handle)
@@ -170,6 +180,26 @@ class Context:
 
     def mem_free(self, ptr: int) -> None:
         self._check(self.lib.kvx_mem_free(self.handle, ptr), "kvx_mem_free")
+
+    def mem_alloc_vmm(self, nbytes: int, piece_bytes: int = 0) -> int:
+        """Device memory from CUDA virtual memory management, exportable as file descriptors (kvx_mem_alloc_vmm)."""
+        out = c_vp()
+        self._check(self.lib.kvx_mem_alloc_vmm(self.handle, nbytes, piece_bytes, ctypes.byref(out)), "kvx_mem_alloc_vmm")
+        return out.value
+
+    def mem_free_vmm(self, ptr: int) -> None:
+        self._check(self.lib.kvx_mem_free_vmm(self.handle, ptr), "kvx_mem_free_vmm")
+
+    def import_pool_fds(self, blob: bytes, fds) -> Pool:
+        """Map a peer's VMM pool from its record and the file descriptors received with it (kvx_pool_import_fds)."""
+        import struct
+
+        arr = (c_i32 * len(fds))(*fds)
+        h = c_vp()
+        self._check(self.lib.kvx_pool_import_fds(self.handle, blob, len(blob), arr, len(fds), ctypes.byref(h)), "kvx_pool_import_fds")
+        (_, regions, N, H, D, E, layout, _, _, _, nb, _) = struct.unpack_from("<10I2Q", blob, 0)
+        return Pool(self, h.value, regions=regions, block_tokens=N, heads=H, head_dim=D, elem_bytes=E, layout=layout,
+                    num_blocks=nb, imported=True)
 
     def mem_export(self, ptr, nbytes: int) -> bytes:
         need = c_sz(0)

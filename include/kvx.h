@@ -172,6 +172,25 @@ int32_t kvx_pool_slice(const kvx_pool* pool, uint32_t first_region, uint32_t cou
  * worker should check this once after registering its pool. */
 int32_t kvx_pool_exportable(kvx_pool* pool, int32_t* across_processes);
 
+/*
+ * Pools in memory that has no CUDA IPC handle: CUDA virtual memory management (cuMemCreate + cuMemMap), which is what an
+ * engine running with expandable segments holds its KV cache in.  Such memory crosses process boundaries as POSIX file
+ * descriptors (one per physical allocation under the pool), which the caller passes over a Unix-domain socket with
+ * SCM_RIGHTS — the pods of the reference's manifests are separate processes (vllm/disagg.yaml:23-25,43-45).
+ * kvx_pool_export_fds writes the record into buf and one fd per allocation into fds (*len / *count: capacity in, size
+ * out; KVX_ERANGE with the needed sizes when too small); the caller sends them and closes its copies.  The memory must
+ * have been created with CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR (torch's expandable segments are; KVX_EIPC otherwise).
+ * kvx_pool_import_fds maps the allocations into this process — allocations that were contiguous in the exporter's
+ * address space stay contiguous — with read/write access for the context's device, and returns a pool like
+ * kvx_pool_import does; kvx_pool_release unmaps.  The fds can be closed after the import.
+ * kvx_mem_alloc_vmm / kvx_mem_free_vmm allocate such memory (in pieces of piece_bytes, 0 = one piece): for engines
+ * that want an exportable VMM pool, and for the tests.
+ */
+int32_t kvx_mem_alloc_vmm(kvx_ctx* ctx, uint64_t bytes, uint64_t piece_bytes, void** out);
+int32_t kvx_mem_free_vmm(kvx_ctx* ctx, void* ptr);
+int32_t kvx_pool_export_fds(kvx_pool* pool, void* buf, size_t* len, int32_t* fds, uint32_t* count);
+int32_t kvx_pool_import_fds(kvx_ctx* ctx, const void* buf, size_t len, const int32_t* fds, uint32_t count, kvx_pool** out);
+
 /* Completion flags: an array of uint64 in this context's device memory that a peer may write
  * (= NIXL notifications, [vllm] worker.py:2164,1792-1845).
  * Limits of flagged transfers (those given a flag, an h_done word or batch notifications): one

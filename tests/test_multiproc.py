@@ -130,3 +130,27 @@ def test_bootstrap_port_pair(tmp_path):
                 proc.kill()
     assert d.returncode == 0 and "decode ok" in d_out, d_out[-3000:]
     assert p.returncode == 0 and "prefill ok" in p_out, p_out[-3000:]
+
+
+@pytest.mark.gpu
+def test_vmm_pool_shared_as_file_descriptors():
+    """A KV pool in CUDA virtual-memory-management memory (no CUDA IPC handle: expandable segments) crosses to another
+    process as file descriptors over a Unix-domain socket, and a request is pulled out of it bit for bit."""
+    import socket
+
+    a, b = socket.socketpair(socket.AF_UNIX, socket.SOCK_STREAM)
+    script = os.path.join(ROOT, "tests", "vmm_pair.py")
+    p = subprocess.Popen([sys.executable, script, "prefill", str(a.fileno())], pass_fds=[a.fileno()], stdout=subprocess.PIPE,
+                         stderr=subprocess.STDOUT, text=True)
+    d = subprocess.Popen([sys.executable, script, "decode", str(b.fileno())], pass_fds=[b.fileno()], stdout=subprocess.PIPE,
+                         stderr=subprocess.STDOUT, text=True)
+    a.close(); b.close()
+    try:
+        d_out, _ = d.communicate(timeout=240)
+        p_out, _ = p.communicate(timeout=60)
+    finally:
+        for proc in (p, d):
+            if proc.poll() is None:
+                proc.kill()
+    assert d.returncode == 0 and "decode ok" in d_out, d_out[-3000:]
+    assert p.returncode == 0 and "prefill ok" in p_out, p_out[-3000:]
