@@ -133,15 +133,22 @@ def test_bootstrap_port_pair(tmp_path):
 
 
 @pytest.mark.gpu
-def test_vmm_pool_shared_as_file_descriptors():
-    """A KV pool in CUDA virtual-memory-management memory (no CUDA IPC handle: expandable segments) crosses to another
-    process as file descriptors over a Unix-domain socket, and a request is pulled out of it bit for bit."""
+@pytest.mark.parametrize("allocator", ["kvx_mem_alloc_vmm", "torch_expandable_segments"])
+def test_vmm_pool_shared_as_file_descriptors(allocator):
+    """A KV pool in CUDA virtual-memory-management memory (no CUDA IPC handle) crosses to another process as file
+    descriptors over a Unix-domain socket, and a request is pulled out of it bit for bit — with the library's own VMM
+    allocator, and with the pool held in a torch tensor under PYTORCH_CUDA_ALLOC_CONF=expandable_segments:True, which is
+    how an engine holds its KV cache."""
     import socket
+
+    env = dict(os.environ)
+    if allocator == "torch_expandable_segments":
+        env["PYTORCH_CUDA_ALLOC_CONF"] = "expandable_segments:True"
 
     a, b = socket.socketpair(socket.AF_UNIX, socket.SOCK_STREAM)
     script = os.path.join(ROOT, "tests", "vmm_pair.py")
     p = subprocess.Popen([sys.executable, script, "prefill", str(a.fileno())], pass_fds=[a.fileno()], stdout=subprocess.PIPE,
-                         stderr=subprocess.STDOUT, text=True)
+                         stderr=subprocess.STDOUT, text=True, env=env)
     d = subprocess.Popen([sys.executable, script, "decode", str(b.fileno())], pass_fds=[b.fileno()], stdout=subprocess.PIPE,
                          stderr=subprocess.STDOUT, text=True)
     a.close(); b.close()

@@ -44,20 +44,26 @@ def main():
     ts, td = o.make_table(NB, N_REQ, 1), o.make_table(NB + 3, N_REQ, 2)
     if role == "prefill":
         nbytes = src_host.buf.nbytes
-        ptr = ctx.mem_alloc_vmm(nbytes, piece_bytes=16 << 20)   # 9 physical allocations, contiguous in the address space
-        synth.as_torch(ptr, nbytes, dev).copy_(torch.from_numpy(src_host.buf))
+        engine_pool = os.environ.get("PYTORCH_CUDA_ALLOC_CONF", "").find("expandable_segments:True") >= 0
+        if engine_pool:   # the KV pool as an engine allocates it: a torch tensor in an expandable segment
+            keep = torch.from_numpy(src_host.buf).cuda()
+            ptr = keep.data_ptr()
+        else:
+            ptr = ctx.mem_alloc_vmm(nbytes, piece_bytes=16 << 20)   # 9 physical allocations, contiguous in the address space
+            synth.as_torch(ptr, nbytes, dev).copy_(torch.from_numpy(src_host.buf))
         torch.cuda.synchronize()
         pool = ctx.register_pool([ptr + off for off in src_host.region_off], num_blocks=NB, heads=H, head_dim=D, layout=kvx.HND)
         assert not pool.exportable_across_processes      # no CUDA IPC handle for this memory ...
         blob, fds = pool.export_fds()                    # ... but file descriptors
-        assert len(fds) == 9, fds
+        assert engine_pool or len(fds) == 9, fds
         send_msg(sock, blob, fds)
         for fd in fds:
             os.close(fd)
         done, _ = recv_msg(sock)
         assert done == b"landed"
         pool.release()
-        ctx.mem_free_vmm(ptr)
+        if not engine_pool:
+            ctx.mem_free_vmm(ptr)
         print(f"prefill ok on cuda:{dev}: {len(fds)} allocations shared as file descriptors", flush=True)
     else:
         blob, fds = recv_msg(sock, max_fds=64)
