@@ -7,14 +7,16 @@
 // first item of request k+1 with the shared-memory ring still full, and the completion of request k is counted
 // off the critical path.
 //
-// Structure of a CTA (blockDim = 32 * (2 + consumer warps)):
+// Structure of a CTA (blockDim = 32 * (3 + consumer warps)):
 //   warp 0   producer — exactly the producer of kvx_xfer_tma_kernel (table lookups 32 items at a time, cp.async.bulk
-//            into the mbarrier ring), in a loop over REQUESTS; it also counts this CTA's part of a request as done
-//            once the consumers have released the request's last stage
-//   warp 1   dispatcher — only in CTA 0: polls the host ring (ld.acquire.sys over PCIe), copies a new request's block
+//            into the mbarrier ring), in a loop over REQUESTS
+//   warp 1   completer — counts this CTA's part of a request as done once the consumers have released the request's
+//            last stage (fence + atomic + the last CTA's notifications: ~1.5 us that neither the producer nor the
+//            consumers wait for); fed by the producer through a small shared-memory FIFO
+//   warp 2   dispatcher — only in CTA 0: polls the host ring (ld.acquire.sys over PCIe), copies a new request's block
 //            ids into the device table ring, publishes it to all CTAs with one release store; decides when the kernel
 //            parks (see below)
-//   warps 2+ consumers — the consumers of kvx_xfer_tma_kernel (shared memory → permuted 16-byte stores), looping
+//   warps 3+ consumers — the consumers of kvx_xfer_tma_kernel (shared memory → permuted 16-byte stores), looping
 //            until they meet the exit marker
 //
 // Parking: a kernel that never ends would block every cudaDeviceSynchronize / cudaFree of the process.  After
@@ -103,7 +105,7 @@ struct TabQueue {
   }
 };
 
-// ---- dispatcher (CTA 0, warp 1) ----------------------------------------------------------------------------
+// ---- dispatcher (CTA 0, warp 2) ----------------------------------------------------------------------------
 __device__ __forceinline__ void queue_dispatch(const QueueParams& q, unsigned lane) {
   unsigned long long seq = q.start[q.gen & 1u];
   unsigned long long t_idle = global_timer_ns();
@@ -216,43 +218,71 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
   const unsigned tid = threadIdx.x;
   const unsigned lane = tid & 31u;
   const unsigned warp = tid >> 5;
-  const unsigned cons_warps = (blockDim.x >> 5) - 2u;
+  const unsigned cons_warps = (blockDim.x >> 5) - 3u;
   const unsigned S = p.stages;
+  // producer → completer FIFO: (slot, stage, parity) of every request's last stage in this CTA
+  constexpr unsigned kCq = 16, kCqNoStage = 0xffu, kCqExit = 0xffffffffu;
+  __shared__ unsigned int cq_slot[kCq], cq_stage[kCq], cq_parity[kCq];
+  __shared__ volatile unsigned int cq_tail, cq_head;
   if (tid == 0) {
     for (unsigned s = 0; s < S; ++s) {
       mbar_init(&full_bar[s], 1u);
       mbar_init(&empty_bar[s], cons_warps);
     }
     mbar_fence_init();
+    cq_tail = 0u;
+    cq_head = 0u;
   }
   __syncthreads();
   const unsigned bid = blockIdx.x;
   const unsigned grid = gridDim.x;
 
-  if (warp == 1) {
+  if (warp == 2) {
     if (bid == 0) queue_dispatch(q, lane);
+    return;
+  }
+  if (warp == 1) {
+    // ------------------------------ completer ------------------------------
+    for (unsigned head = 0;; ++head) {
+      while (cq_tail == head) __nanosleep(64);   // idle until the producer queues a completion (or the exit entry at the park)
+      __threadfence_block();
+      const unsigned slot = cq_slot[head % kCq], stage = cq_stage[head % kCq], parity = cq_parity[head % kCq];
+      if (slot == kCqExit) break;
+      if (stage != kCqNoStage) mbar_wait(&empty_bar[stage], parity);  // every consumer warp has stored this CTA's last piece of the request
+      if (lane == 0) {
+        const QueueDesc d = load_desc_full(q.desc + slot);
+        queue_count_done(q, d, slot);
+      }
+      __syncwarp();
+      if (lane == 0) cq_head = head + 1u;
+    }
     return;
   }
   if (warp == 0) {
     // ------------------------------ producer: a loop over requests ------------------------------
-    // Completions wait in a FIFO until the consumers have released the request's last stage; an entry is always
-    // popped before its stage is filled again (the drain right after every wait for a free stage), so the
-    // barrier's parity cannot wrap under it.
-    struct Pending { unsigned slot, stage, parity; };
-    Pending pend[kMaxStages + 1];
-    unsigned pend_head = 0, pend_n = 0;
-    auto drain = [&](bool block) {
-      while (pend_n != 0) {
-        const Pending e = pend[pend_head];
-        if (block) mbar_wait(&empty_bar[e.stage], e.parity);
-        else if (!mbar_try_wait(&empty_bar[e.stage], e.parity)) break;
-        if (lane == 0) {
-          const QueueDesc d = load_desc_full(q.desc + e.slot);
-          queue_count_done(q, d, e.slot);
-        }
-        pend_head = (pend_head + 1u) % (kMaxStages + 1u);
-        --pend_n;
+    // A request's completion goes to the completer as (slot, last stage, that fill's parity).  The completer must see the
+    // release of that fill before the stage is filled AGAIN (two phases on, the barrier's parity would read the same):
+    // guard[s] remembers the FIFO position of the entry that names stage s, and the producer does not refill s before the
+    // completer is past it.
+    unsigned cq_pushed = 0;
+    unsigned guard[kMaxStages];
+#pragma unroll
+    for (unsigned k = 0; k < kMaxStages; ++k) guard[k] = 0u;
+    auto spin_until_head = [&](unsigned want) {
+      if (cq_head >= want) return;
+      const unsigned long long t0 = global_timer_ns();
+      for (unsigned spins = 1; cq_head < want; ++spins)
+        if ((spins & 0xffu) == 0 && global_timer_ns() - t0 > 4000000000ull) __trap();
+    };
+    auto push = [&](unsigned slot, unsigned stage, unsigned parity) {
+      if (cq_pushed >= kCq) spin_until_head(cq_pushed - kCq + 1u);
+      if (lane == 0) {
+        cq_slot[cq_pushed % kCq] = slot; cq_stage[cq_pushed % kCq] = stage; cq_parity[cq_pushed % kCq] = parity;
+        __threadfence_block();
+        cq_tail = cq_pushed + 1u;
       }
+      ++cq_pushed;
+      if (stage != kCqNoStage) guard[stage] = cq_pushed;
     };
     unsigned long long seq = q.start[q.gen & 1u];
     unsigned long long pub_known = 0;  // requests known to be published (saves the poll when several were published at once)
@@ -267,14 +297,21 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
         dn = d->n; dtab = d->tab_off; dtotal = d->total_items;
       }
     };
+    // Items are dealt to the CTAs round robin ACROSS requests: request k+1's first item goes to the CTA after the one
+    // that got request k's last, so no CTA is always the one with the extra item (at 8 blocks per request that extra
+    // item is a sixth of a CTA's work).  `rot` = items dealt so far mod grid, `e` = this CTA's place in the current deal.
+    unsigned rot = 0, e = bid;
+    rp.total_items = 0;
     auto adopt = [&](unsigned dn, unsigned dtab, unsigned dtotal) {
       dn = __shfl_sync(0xffffffffu, dn, 0);
       dtab = __shfl_sync(0xffffffffu, dtab, 0);
       dtotal = __shfl_sync(0xffffffffu, dtotal, 0);
+      rot = (rot + rp.total_items % grid) % grid;   // the request that was in rp has been dealt
+      e = (bid + grid - rot) % grid;
       rp.n = dn; rp.total_items = dtotal;
       rp.src.tab_off = dtab; rp.dst.tab_off = dtab + dn;
-      const unsigned items = bid < dtotal ? (dtotal - bid + grid - 1u) / grid : 0u;
-      if (lane < items) item_load(rp, tab, bid + lane * grid, raw);
+      const unsigned items = e < dtotal ? (dtotal - e + grid - 1u) / grid : 0u;
+      if (lane < items) item_load(rp, tab, e + lane * grid, raw);
     };
     for (;;) {
       if (!primed) {
@@ -290,7 +327,6 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
           pk = __shfl_sync(0xffffffffu, pk, 0);
           __syncwarp();  // lane 0's acquire orders the other lanes' table and descriptor loads behind the publication
           if (pub_known > seq) break;
-          drain(false);
           if ((pk >> 40) == q.gen && seq >= (pk & ((1ull << 40) - 1))) { leave = true; break; }
           __nanosleep(100);
         }
@@ -302,7 +338,8 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
       primed = false;
       const unsigned slot = static_cast<unsigned>(seq & q.ring_mask);
       const unsigned dtotal = rp.total_items;
-      const unsigned my_items = bid < dtotal ? (dtotal - bid + grid - 1u) / grid : 0u;
+      const unsigned my_items = e < dtotal ? (dtotal - e + grid - 1u) / grid : 0u;
+      const unsigned e_cur = e;   // adopt() moves e on to the next request while this one's last batch is being issued
       unsigned last_stage = 0, last_parity = 0;
       for (unsigned base = 0; base < my_items; base += 32u) {
         unsigned long long sa = 0, da = 0;
@@ -312,7 +349,7 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
         unsigned ndn = 0, ndtab = 0, ndtotal = 0;
         bool next_ready = false;
         if (!last_batch) {
-          if (base + 32u + lane < my_items) item_load(rp, tab, bid + (base + 32u + lane) * grid, raw);
+          if (base + 32u + lane < my_items) item_load(rp, tab, e_cur + (base + 32u + lane) * grid, raw);
         } else {
           // Last batch of this request: while it is being issued, fetch the next request's descriptor (and below its
           // first table lookups), so that the ring does not run dry between two requests.
@@ -331,7 +368,10 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
           const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
           const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
           mbar_wait(&empty_bar[s], phase ^ 1u);
-          drain(false);
+          if (guard[s] != 0u) {  // the completer has to be past this stage's last completion entry before the refill
+            spin_until_head(guard[s]);
+            guard[s] = 0u;
+          }
           unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
           if (lane == 0) {
             meta_dst[s] = dst;
@@ -356,20 +396,14 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
           primed = true;
         }
       }
-      if (my_items == 0) {
-        if (lane == 0) {  // nothing of this request falls to this CTA: it still counts
-          const QueueDesc d = load_desc_full(q.desc + slot);
-          queue_count_done(q, d, slot);
-        }
-      } else {
-        pend[(pend_head + pend_n) % (kMaxStages + 1u)] = Pending{slot, last_stage, last_parity};
-        ++pend_n;
-      }
+      // nothing of a request may fall to this CTA (fewer items than CTAs): it still counts
+      push(slot, my_items == 0 ? kCqNoStage : last_stage, last_parity);
       ++seq;
     }
-    drain(true);
+    push(kCqExit, kCqNoStage, 0u);
     // exit marker for the consumers
     mbar_wait(&empty_bar[s], phase ^ 1u);
+    if (guard[s] != 0u) spin_until_head(guard[s]);
     if (lane == 0) {
       meta_bytes[s] = kQueueExit;
       mbar_arrive_expect_tx(&full_bar[s], 0u);
@@ -377,8 +411,8 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
     return;
   }
   // ------------------------------ consumers ------------------------------
-  const unsigned ctid = tid - 64u;
-  const unsigned T = blockDim.x - 64u;
+  const unsigned ctid = tid - 96u;
+  const unsigned T = blockDim.x - 96u;
   unsigned doff[KMAX];
   const unsigned upr = p.d_run_bytes / VEC;
 #pragma unroll

@@ -121,7 +121,7 @@ int32_t kvx_queue_start(kvx_ctx* ctx, const kvx_pool* src, const kvx_pool* dst, 
   kvx_queue* q = new (std::nothrow) kvx_queue();
   if (!q) return KVX_ENOMEM;
   q->ctx = ctx; q->src = src; q->dst = dst;
-  q->block = 32u * (2u + g.cons_warps);
+  q->block = 32u * (3u + g.cons_warps);
   q->smem = static_cast<size_t>(g.stages) * g.stage_bytes;
   auto fail = [&](int32_t code) {
     queue_free(q);
