@@ -341,18 +341,36 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
       const unsigned my_items = e < dtotal ? (dtotal - e + grid - 1u) / grid : 0u;
       const unsigned e_cur = e;   // adopt() moves e on to the next request while this one's last batch is being issued
       unsigned last_stage = 0, last_parity = 0;
+      // The chain "is the next request published → its descriptor → its first table lookups" is three dependent L2 round
+      // trips; it runs BEHIND this request's own work so that the ring does not run dry between two requests: the
+      // descriptor loads are issued here, before the first piece of this request, and consumed in the last batch.
+      unsigned ndn = 0, ndtab = 0, ndtotal = 0;
+      bool early = false;
+      if (my_items != 0) {
+        if (pub_known <= seq + 1) {
+          unsigned long long pub = 0;
+          if (lane == 0) pub = ld_acquire_gpu(q.pub_seq);
+          pub_known = __shfl_sync(0xffffffffu, pub, 0);
+          __syncwarp();
+        }
+        early = pub_known > seq + 1;
+        if (early) load_desc(seq + 1, ndn, ndtab, ndtotal);
+      }
       for (unsigned base = 0; base < my_items; base += 32u) {
         unsigned long long sa = 0, da = 0;
         unsigned bytes = 0;
         if (base + lane < my_items) item_finish(rp, raw, sa, da, bytes);
         const bool last_batch = base + 32u >= my_items;
-        unsigned ndn = 0, ndtab = 0, ndtotal = 0;
         bool next_ready = false;
         if (!last_batch) {
           if (base + 32u + lane < my_items) item_load(rp, tab, e_cur + (base + 32u + lane) * grid, raw);
+        } else if (early) {
+          // every use of rp and raw for THIS request lies behind us (only addresses in registers are issued below): make
+          // them the next request's and put its first table lookups in flight under this batch's bulk copies
+          adopt(ndn, ndtab, ndtotal);
+          primed = true;
         } else {
-          // Last batch of this request: while it is being issued, fetch the next request's descriptor (and below its
-          // first table lookups), so that the ring does not run dry between two requests.
+          // the next request was not there when this one started: look once more, fetch its descriptor under this batch
           if (pub_known <= seq + 1) {
             unsigned long long pub = 0;
             if (lane == 0) pub = ld_acquire_gpu(q.pub_seq);
@@ -391,7 +409,7 @@ __global__ void kvx_queue_kernel(const __grid_constant__ QueueParams q) {
           last_stage = s; last_parity = phase;
           if (++s == S) { s = 0; phase ^= 1u; }
         }
-        if (next_ready) {  // every use of rp for THIS request lies behind us: make it the next request's
+        if (next_ready) {
           adopt(ndn, ndtab, ndtotal);
           primed = true;
         }
