@@ -775,6 +775,9 @@ def run_pairs(args):
             rec["queue_ctas"] = q.ctas
             q.park()
             torch.cuda.synchronize()
+        # the prefill ranks wait here on the CPU (gloo): an NCCL collective would park a spinning kernel on the very GPUs
+        # whose memory is being read
+        dist.all_reduce(torch.zeros(1))
         allr = [None] * world
         dist.all_gather_object(allr, rec)
         if rank == 0:
