@@ -266,6 +266,7 @@ struct LaunchSpec {  // what a transfer needs besides geometry
   uint32_t notify_count = 0;
   bool block_major = false;  // visit items block by block (cross-layer pools)
   const kvx_pool* dst_pool = nullptr;  // paged destination as a pool (tensor-map engine)
+  const kvx_pool* src_pool = nullptr;  // paged source as a pool (tensor-map engine, load side)
 };
 
 // int32 entries of the parameter table area a launch needs: both sides' ids, then the notifications
@@ -516,6 +517,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.n = ls.n;
   p.regions = ls.regions;
   Plan pl{};
+  const void* tmap_load_maps = nullptr;
   if (ls.copy_mode) {
     uint32_t piece = engine == kEngineTma ? stage_cap : ldg_cap16;
     if (engine == kEngineTma && store_mode == 1 && ctx->opt[KVX_OPT_CONSUMER_WARPS] > 0)
@@ -532,9 +534,21 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     const uint64_t tail = ls.copy_bytes - (items - 1) * piece;
     p.tail_bytes = tail == piece ? 0u : static_cast<uint32_t>(tail);
   } else {
-    int32_t rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, engine == kEngineTma ? stage_cap : ldg_cap16, &pl);
+    // store_mode 3 with an NHD source and an HND destination: the permutation moves to the LOAD side (one tensor-map load
+    // per head lands the piece head-major in shared memory), so the piece is planned as if the source were HND
+    ChunkGeom sg = ls.sg;
+    if (engine == kEngineTma && store_mode == 3 && ls.src_pool != nullptr && ls.h_src_tab == nullptr && ls.notify_count == 0 &&
+        ls.sg.layout == KVX_LAYOUT_NHD && ls.dg.layout == KVX_LAYOUT_HND && ls.sg.nb == ls.N && ls.dg.nb == ls.N &&
+        pool_tensor_maps(ctx, ls.src_pool, &tmap_load_maps) == KVX_OK) {
+      sg.layout = KVX_LAYOUT_HND;
+      sg.hs = 0;
+    } else {
+      tmap_load_maps = nullptr;
+    }
+    int32_t rc = make_plan(ls.N, ls.R, ls.Hc, sg, ls.dg, engine == kEngineTma ? stage_cap : ldg_cap16, &pl);
     if (rc == KVX_EUNSUPPORTED && engine == kEngineTma) {  // unit larger than a stage: register path
       engine = kEngineLdg;
+      tmap_load_maps = nullptr;
       rc = make_plan(ls.N, ls.R, ls.Hc, ls.sg, ls.dg, ldg_cap16, &pl);
     }
     if (rc != KVX_OK) return rc;
@@ -608,6 +622,18 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
                            ctx->opt[KVX_OPT_STAGES] == 0 && ctx->opt[KVX_OPT_STAGE_BYTES] == 0 && ctx->opt[KVX_OPT_CONSUMER_WARPS] == 0 &&
                            ctx->opt[KVX_OPT_VEC_BYTES] == 0;
     const bool tmap_case = (store_mode == 3 && tmap_shape) || tmap_auto;
+    if (tmap_load_maps != nullptr) {
+      p.src_tmaps = tmap_load_maps;
+      p.tm_head_bytes = ls.N * ls.R;
+      p.tm_head0 = ls.sg.off;
+      auto k = kvx::kvx_xfer_tmapld_kernel;
+      int32_t rc = set_smem(ctx, k, smem);
+      if (rc) return rc;
+      KVX_CUDA(ctx, launch_kernel(k, grid, 64u, smem, stream, pdl, p));
+      KVX_CUDA(ctx, cudaGetLastError());
+      ctx->launches++;
+      return KVX_OK;
+    }
     if (tmap_case) {
       const void* maps = nullptr;
       int32_t rc = pool_tensor_maps(ctx, ls.dst_pool, &maps);
@@ -932,6 +958,7 @@ int32_t handoff_impl(kvx_ctx* ctx, const kvx_pool* src, const int32_t* d_src_tab
   ls.flag2 = flag2;
   ls.block_major = regions_inside_one_block(*src) || regions_inside_one_block(*dst);
   ls.dst_pool = dst;
+  ls.src_pool = src;
   ls.dst_is_peer = !dst->local;
   ls.dst_is_peer_known = ls.dst_is_peer;
   ls.src_is_peer = !src->local;

@@ -68,6 +68,7 @@ struct XferParams {
   // Tensor-map engine (kvx_xfer_tmap_kernel): one CUtensorMap per destination region over [block][N][H][row],
   // the permutation HND → NHD done by the TMA unit: one box store per head of a piece.
   const void* dst_tmaps;       // device array [regions] of CUtensorMap (128 bytes each), or null
+  const void* src_tmaps;       // the same for an NHD SOURCE pool (kvx_xfer_tmapld_kernel: NHD → HND, permutation on the load side)
   unsigned int tm_head_bytes;  // bytes of one head's slab in the shared-memory image: N * row
   unsigned int tm_head0;       // first destination head of piece 0 (TP slot); piece k starts at tm_head0 + k * heads per piece
 };
@@ -150,6 +151,14 @@ __device__ __forceinline__ void tensor_s2g_4d(const void* tmap, const void* smem
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
                    reinterpret_cast<unsigned long long>(tmap)),
                "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+// TMA tensor load global → shared through a 4-d tensor map, completion counted in bytes on an mbarrier (one CTA's
+// own shared memory; never multicast).
+__device__ __forceinline__ void tensor_g2s_4d(void* smem_dst, const void* tmap, int c0, int c1, int c2, int c3, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+                   smem_u32(smem_dst)),
+               "l"(reinterpret_cast<unsigned long long>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
 template <int N>
@@ -627,6 +636,99 @@ __device__ __forceinline__ void xfer_tmap_body(const XferParams& p, const Tab ta
 
 __global__ void __launch_bounds__(64) kvx_xfer_tmap_kernel(const __grid_constant__ XferParams p) {
   xfer_tmap_body(p, TabGlobal{});
+}
+
+// The other direction, NHD source → HND destination: the producer fetches every head of a piece with one
+// cp.async.bulk.tensor LOAD (box = that head's N rows of one block of the source region), which lands them head-major in
+// shared memory; the second warp writes the piece out with plain bulk stores (one per destination run).
+__global__ void __launch_bounds__(64) kvx_xfer_tmapld_kernel(const __grid_constant__ XferParams p) {
+  extern __shared__ __align__(1024) unsigned char stage_mem[];
+  __shared__ __align__(8) unsigned long long full_bar[kMaxStages];
+  __shared__ __align__(8) unsigned long long empty_bar[kMaxStages];
+  __shared__ unsigned long long meta_dst[kMaxStages];
+  __shared__ unsigned int meta_bytes[kMaxStages];
+  const TabGlobal tab{};
+  const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  const unsigned S = p.stages;
+  grid_dep_launch_dependents();
+  if (tid == 0) {
+    for (unsigned s = 0; s < S; ++s) {
+      mbar_init(&full_bar[s], 1u);
+      mbar_init(&empty_bar[s], 1u);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const unsigned bid = blockIdx.x, grid = gridDim.x;
+  const unsigned my_items = bid < p.total_items ? (p.total_items - bid + grid - 1u) / grid : 0u;
+  const unsigned heads_per_piece = p.piece_bytes / p.tm_head_bytes;
+  if (warp == 0) {
+    grid_dep_wait();
+    RawItem raw{};
+    if (lane < my_items) item_load(p, tab, bid + lane * grid, raw);
+    unsigned s = 0, phase = 0;
+    for (unsigned base = 0; base < my_items; base += 32u) {
+      unsigned long long sa = 0, da = 0;
+      unsigned bytes = 0;
+      if (base + lane < my_items) item_finish(p, raw, sa, da, bytes);
+      const int my_blk = raw.s.id;
+      const unsigned my_reg = raw.r, my_piece = raw.piece;
+      if (base + 32u + lane < my_items) item_load(p, tab, bid + (base + 32u + lane) * grid, raw);
+      const unsigned cnt = min(32u, my_items - base);
+      for (unsigned j = 0; j < cnt; ++j) {
+        const unsigned long long dst = __shfl_sync(0xffffffffu, da, j);
+        const unsigned nbytes = __shfl_sync(0xffffffffu, bytes, j);
+        const int blk = __shfl_sync(0xffffffffu, my_blk, j);
+        const unsigned reg = __shfl_sync(0xffffffffu, my_reg, j);
+        const unsigned piece = __shfl_sync(0xffffffffu, my_piece, j);
+        mbar_wait(&empty_bar[s], phase ^ 1u);
+        unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+        if (lane == 0) {
+          meta_dst[s] = dst;
+          meta_bytes[s] = nbytes;
+          mbar_arrive_expect_tx(&full_bar[s], nbytes);
+        }
+        __syncwarp();
+        if (nbytes != 0) {
+          const unsigned char* tm = static_cast<const unsigned char*>(p.src_tmaps) + static_cast<size_t>(reg) * 128u;
+          const unsigned head0 = p.tm_head0 + piece * heads_per_piece;
+          for (unsigned h = lane; h < heads_per_piece; h += 32u)
+            tensor_g2s_4d(stage + static_cast<size_t>(h) * p.tm_head_bytes, tm, 0, static_cast<int>(head0 + h), 0, blk, &full_bar[s]);
+        }
+        if (++s == S) { s = 0; phase ^= 1u; }
+      }
+    }
+  } else {
+    unsigned prev_stage = 0;
+    bool have_prev = false;
+    grid_dep_wait();
+    unsigned s = 0, phase = 0;
+    for (unsigned it = 0; it < my_items; ++it) {
+      mbar_wait(&full_bar[s], phase);
+      const unsigned long long dst = meta_dst[s];
+      const unsigned nbytes = meta_bytes[s];
+      const unsigned char* stage = stage_mem + static_cast<size_t>(s) * p.stage_bytes;
+      if (nbytes != 0) {
+        if (p.d_runs == 1u) {
+          if (lane == 0) bulk_s2g(dst, stage, nbytes);
+        } else {
+          for (unsigned x = lane; x < p.d_runs; x += 32u)
+            bulk_s2g(dst + dst_run_offset(p, x), stage + x * p.d_run_bytes, p.d_run_bytes);
+        }
+      }
+      bulk_commit();
+      if (have_prev) {
+        bulk_wait_read<1>();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty_bar[prev_stage]);
+      }
+      prev_stage = s;
+      have_prev = true;
+      if (++s == S) { s = 0; phase ^= 1u; }
+    }
+    bulk_wait<0>();
+  }
+  finish_and_flag(p, tab);
 }
 
 // ----------------------------------------------------------------------------------------------

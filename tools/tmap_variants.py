@@ -47,16 +47,21 @@ VARIANTS = [
 
 
 def local_cases():
-    for model, heads, isl in (("Qwen/Qwen3-0.6B", 8, 8192), ("Qwen/Qwen3-0.6B", 8, 1024), ("meta-llama/Llama-3.1-70B", 2, 8192),
-                              ("meta-llama/Llama-3.1-70B", 1, 8192)):
+    cases = [("Qwen/Qwen3-0.6B", 8, 8192, kvx.HND, kvx.NHD), ("Qwen/Qwen3-0.6B", 8, 1024, kvx.HND, kvx.NHD),
+             ("meta-llama/Llama-3.1-70B", 2, 8192, kvx.HND, kvx.NHD), ("meta-llama/Llama-3.1-70B", 1, 8192, kvx.HND, kvx.NHD),
+             # the other direction: tensor-map LOADS (NHD source), plain bulk stores
+             ("Qwen/Qwen3-0.6B", 8, 8192, kvx.NHD, kvx.HND), ("meta-llama/Llama-3.1-70B", 2, 8192, kvx.NHD, kvx.HND)]
+    if os.environ.get("DIRECTION") == "nhd_to_hnd":
+        cases = cases[4:]
+    for model, heads, isl, lay_s, lay_d in cases:
         shape = kvx.KV_SHAPES[model]
         n = shape.blocks_for(isl)
         nb = 4 * n + 1
         ref = None
         for opts in VARIANTS:
             ctx = kvx.Context(0, **opts)
-            P = synth.alloc_pool(ctx, shape, nb, kvx.HND, heads=heads)
-            D = synth.alloc_pool(ctx, shape, nb, kvx.NHD, heads=heads)
+            P = synth.alloc_pool(ctx, shape, nb, lay_s, heads=heads)
+            D = synth.alloc_pool(ctx, shape, nb, lay_d, heads=heads)
             synth.fill_random(P, 11)
             synth.fill_canary(D)
             tp, td = synth.make_table(nb, 4 * n, 1), synth.make_table(nb, 4 * n, 2)
@@ -70,7 +75,7 @@ def local_cases():
                 got = D.tensor().clone()
                 if ref is None:
                     ref = got
-                print(json.dumps({"case": "one GPU, fused HND->NHD", "model": model, "heads": heads, "isl": isl, "chunk_KiB": chunk // 1024,
+                print(json.dumps({"case": "one GPU, fused " + ("HND->NHD" if lay_s == kvx.HND else "NHD->HND"), "model": model, "heads": heads, "isl": isl, "chunk_KiB": chunk // 1024,
                                   "opts": opts or "default (thread stores)", "us": round(1e3 * t, 1), "hbm_GBps": round(2 * payload / t / 1e6, 1),
                                   "bit_exact_vs_default": bool(torch.equal(got, ref))}), flush=True)
             except kvx.KvxError as e:
