@@ -518,6 +518,7 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
   p.regions = ls.regions;
   Plan pl{};
   const void* tmap_load_maps = nullptr;
+  bool tmap_load_auto = false;
   if (ls.copy_mode) {
     uint32_t piece = engine == kEngineTma ? stage_cap : ldg_cap16;
     if (engine == kEngineTma && store_mode == 1 && ctx->opt[KVX_OPT_CONSUMER_WARPS] > 0)
@@ -537,7 +538,13 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
     // store_mode 3 with an NHD source and an HND destination: the permutation moves to the LOAD side (one tensor-map load
     // per head lands the piece head-major in shared memory), so the piece is planned as if the source were HND
     ChunkGeom sg = ls.sg;
-    if (engine == kEngineTma && store_mode == 3 && ls.src_pool != nullptr && ls.h_src_tab == nullptr && ls.notify_count == 0 &&
+    // (store_mode 0 takes this path by itself for the case it measured faster in: whole 8 KiB chunks of two or more heads on
+    // one GPU, 6.35 against 5.95 TB/s — the mirror image of the store-side rule further down)
+    const bool load_auto = store_mode == 0 && !remote && static_cast<uint64_t>(ls.Hc) * ls.N * ls.R == 8192u && ls.N * ls.R <= 4096u &&
+                           ctx->opt[KVX_OPT_STAGES] == 0 && ctx->opt[KVX_OPT_STAGE_BYTES] == 0 && ctx->opt[KVX_OPT_CONSUMER_WARPS] == 0 &&
+                           ctx->opt[KVX_OPT_VEC_BYTES] == 0;
+    tmap_load_auto = load_auto;
+    if (engine == kEngineTma && (store_mode == 3 || load_auto) && ls.src_pool != nullptr && ls.h_src_tab == nullptr && ls.notify_count == 0 &&
         ls.sg.layout == KVX_LAYOUT_NHD && ls.dg.layout == KVX_LAYOUT_HND && ls.sg.nb == ls.N && ls.dg.nb == ls.N &&
         pool_tensor_maps(ctx, ls.src_pool, &tmap_load_maps) == KVX_OK) {
       sg.layout = KVX_LAYOUT_HND;
@@ -629,7 +636,10 @@ int32_t launch_xfer(kvx_ctx* ctx, const LaunchSpec& ls, const std::vector<void*>
       auto k = kvx::kvx_xfer_tmapld_kernel;
       int32_t rc = set_smem(ctx, k, smem);
       if (rc) return rc;
-      KVX_CUDA(ctx, launch_kernel(k, grid, 64u, smem, stream, pdl, p));
+      uint32_t tgrid = grid;
+      if (tmap_load_auto && ctx->opt[KVX_OPT_CTAS_PER_SM] == 0 && ctx->opt[KVX_OPT_MAX_CTAS] == 0)
+        tgrid = std::min<uint32_t>(static_cast<uint32_t>(ctx->sms) * 2u, p.total_items);
+      KVX_CUDA(ctx, launch_kernel(k, tgrid, 64u, smem, stream, pdl, p));
       KVX_CUDA(ctx, cudaGetLastError());
       ctx->launches++;
       return KVX_OK;

@@ -55,9 +55,11 @@ enum {
   KVX_OPT_CTAS_PER_SM = 3, /* persistent grid = SMs x this; 0 (default) = 1 (3 for pieces of 8 KiB or
                               less, 2 for the register engine)                                 */
   KVX_OPT_STORE_MODE = 4,  /* tma: 0 auto, 1 thread stores, 2 bulk stores (one per destination run), 3 tensor-map
-                              stores (cp.async.bulk.tensor: one box store per head, the TMA unit does the
-                              HND->NHD permutation, 2 warps per CTA; only HND chunks into an NHD pool of the
-                              same block size with device tables — other transfers use thread stores)   */
+                              engine (cp.async.bulk.tensor: the TMA unit does the permutation, 2 warps per
+                              CTA): one box STORE per head for HND chunks into an NHD pool, one box LOAD per
+                              head for NHD chunks into an HND pool; same block size on both sides, device
+                              tables — other transfers use thread stores.  0 picks it by itself for 8 KiB
+                              chunks of two or more heads on one GPU, where it measured ~6 % faster        */
   KVX_OPT_VEC_BYTES = 5,   /* thread path: 16 or 32 byte accesses (0 auto)                   */
   KVX_OPT_CONSUMER_WARPS = 6, /* tma: consumer warps per CTA (1..16); 0 (default) = 16, or 4 when a
                                  piece is 8 KiB or less (chunks of TP shards)                    */
