@@ -980,6 +980,9 @@ def run_pairs(args):
             phase("leg config5 mixed ISL")
             cfg = harness.StreamConfig(model=M8, isl=per_rep[0], per_replica_isl=per_rep, concurrency=1)
             legs["config5_mixed_isl"] = brief(harness_leg(dist, rank, world, topo, cfg, n_devices=ndev))
+            phase("leg config5 mixed ISL through the resident receiver")
+            cfg = harness.StreamConfig(model=M8, isl=per_rep[0], per_replica_isl=per_rep, concurrency=1, queue=True)
+            legs["config5_mixed_isl_resident_receiver"] = brief(harness_leg(dist, rank, world, topo, cfg, n_devices=ndev), extra=("resident_receiver",))
         # config #4's: TP reshard on transfer, prefill TP = 2 x decode TP, every edge concurrent.  6 of 8 GPUs run
         # TP4 -> TP2 (Llama-3.1-70B); with 4 GPUs the same code runs TP2 -> TP1 on 3 of them.
         if world >= 4 and ("all" in want or "config4" in want):

@@ -8,6 +8,7 @@ transport URL:  kvx://local?manifest=<DynamoGraphDeployment yaml>[&isl=8192][&re
            kvx://local?prefill=4&decode=4[&ptp=4&dtp=2][&isl=1024,2048,...][&layout=nhd][&route=spread][&batch=8]
            ...&arrival=bursty[&gap_ms=1.0][&burst=4]&route=sched   one bursty stream, booked by kvx/router.py
            ...&layerwise=8&prefill_ms=20                            hand over in 8 layer groups behind a synthetic prefill
+           ...&queue=1                                              pull through the resident receiver (kvx_queue_*)
 Every request is verified bit for bit unless verify=0 is given; an unverified run says so and is never "verified".
 Results land under <output-dir>/<benchmark-name>/results.json; -p adds SVG plots from that tree.
 """
@@ -113,7 +114,7 @@ def build_job(url: str, model: str):
     cfg = StreamConfig(model=model, isl=isl, concurrency=int(q.get("concurrency", 1)), verify=q.get("verify", "1") != "0",
                        decode_layout=layout, options=opts, route=q.get("route", "pair"), batch=int(q.get("batch", 1)),
                        ready_ms=ready, per_replica_isl=per_rep, layerwise=int(q.get("layerwise", 1)),
-                       prefill_ms=float(q.get("prefill_ms", 0.0)), corrupt=corrupt)
+                       prefill_ms=float(q.get("prefill_ms", 0.0)), corrupt=corrupt, queue=q.get("queue", "0") == "1")
     return topo, cfg
 
 

@@ -57,6 +57,7 @@ class StreamConfig:
     ready_ms: Optional[List[float]] = None  # arrival-driven: when each request's KV is ready (prefill done), from stream start
     layerwise: int = 1        # > 1: hand each request over in this many layer groups, each as soon as it is "prefilled"
     prefill_ms: float = 0.0   # layerwise: synthetic prefill time of one request on the prefill GPU (spread over its layers)
+    queue: bool = False       # pull through the resident receiver (kvx_queue_*: no launch per request); same-size TP, not layer-wise
     corrupt: Optional[Tuple[int, int]] = None  # test hook: flip one byte of request (decode replica, index) after it landed
 
 
@@ -248,7 +249,8 @@ class _Verifier:
     def check_request(self, after, remote: Dict[int, np.ndarray], local_ids, edges, corrupt: bool = False):
         """Queue the check of one landed request behind event `after`; returns the event that marks the check done."""
         torch = self.torch
-        self.stream.wait_event(after)
+        if after is not None:   # None: the host has already seen the request complete (resident receiver)
+            self.stream.wait_event(after)
         with torch.cuda.stream(self.stream):
             if corrupt and len(local_ids):
                 self.dv[self.shape.regions // 2, int(local_ids[len(local_ids) // 2]), 5] ^= 1
@@ -410,9 +412,24 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
                 cons = consumers_of(e.p_rank)
                 return _release_slot(mine[i].p_serial, cons.index(me.tp_rank), len(cons), w.remotes[mine[i].p_rep * 1000 + e.p_rank].meta.num_flags)
 
+            use_queue = cfg.queue and cfg.batch <= 1 and len(srcs) == 1 and p_tp == d_tp and not gated
+            tickets: Dict[int, int] = {}
+
             def issue(i: int, lane) -> None:
                 """Queue request i on a lane: one pull per source edge (fan-in when p_tp > d_tp), joined on lane[0]."""
                 r = mine[i]
+                if use_queue:
+                    # the receiver runs on a stream of its own: the checks that must have read the blocks this request
+                    # reuses are waited for on the host, and completion is the request's ticket
+                    limit = i - hold - 1
+                    if ver is not None and limit >= 0:
+                        while prefix["upto"] < limit:
+                            prefix["upto"] += 1
+                            prefix["pos"] = max(prefix["pos"], chk_pos[prefix["upto"]])
+                        chk_events[prefix["pos"]].synchronize()
+                    tickets[i] = w.pull_queued(r.p_rep * 1000 + srcs[0].p_rank, remote_ids[i], local_ids[i],
+                                               notify_slot=flag_slot(i, srcs[0]), value=val_of(r))
+                    return
                 wait_for_checks(i, lane)
                 ev[i][0].record(lane[0])
                 for j, e in enumerate(srcs):
@@ -439,7 +456,7 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
 
             def landed(i: int) -> None:
                 if ver is not None:
-                    chk_events.append(ver.check_request(ev[i][1], remote_of(i), local_ids[i], edges_of(i),
+                    chk_events.append(ver.check_request(None if use_queue else ev[i][1], remote_of(i), local_ids[i], edges_of(i),
                                                         corrupt=cfg.corrupt is not None and tuple(cfg.corrupt) == (me.replica, i)))
                     chk_pos[i] = len(chk_events) - 1
                 checked_args[i] = (remote_of(i), local_ids[i], edges_of(i))
@@ -475,7 +492,7 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
                 while nxt < len(mine) or inflight:
                     progressed = False
                     for i in list(inflight):
-                        if ev[i][1].query():
+                        if (w.pull_queue(mine[i].p_rep * 1000 + srcs[0].p_rank).poll(tickets[i]) if use_queue else ev[i][1].query()):
                             t_done[i] = time.perf_counter()
                             free_lanes.append(inflight.pop(i))
                             landed(i)
@@ -492,8 +509,12 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
                         wait = mine[nxt].ready_ms - now_ms()
                         if wait > 0.2:
                             time.sleep((wait - 0.1) / 1e3)
+            t_end = time.perf_counter() if use_queue else None   # every ticket has been seen: nothing is in flight
+            if use_queue:
+                for q_ in w.__dict__.get("_queues", {}).values():
+                    q_.park()
             torch.cuda.synchronize()
-            t_end = time.perf_counter()
+            t_end = t_end or time.perf_counter()
             w.ctx.check()
             per_req = []
             for i, r in enumerate(mine):
@@ -503,6 +524,10 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
                     xfer = ev[g0][0].elapsed_time(ev[g0][1]) / 1e3
                     rate = sum(mine[x].n for x in qs) * shape.regions * chunk_d / xfer / 1e9
                     ttft = 1e3 * (t_done[i] - t_sub[i])
+                elif use_queue:   # no launch to bracket with events: host clock, submit -> ticket seen
+                    xfer = t_done[i] - t_sub[i]
+                    rate = b / xfer / 1e9 if xfer > 0 else 0.0
+                    ttft = 1e3 * (t_done[i] - t_ready[i])
                 else:
                     xfer = ev[i][0].elapsed_time(ev[i][1]) / 1e3
                     rate = b / xfer / 1e9 if xfer > 0 else 0.0
@@ -621,7 +646,7 @@ def summarize(ranks: List[Dict], topo_desc: Dict, cfg: StreamConfig, world: int,
     ver = [r["verification"] for r in dec if r.get("verification")]
     summary = {
         "topology": topo_desc, "model": asdict(shape), "isl": sorted(by_isl), "concurrency": cfg.concurrency,
-        "route": cfg.route, "layerwise": cfg.layerwise, "arrival_driven": cfg.ready_ms is not None,
+        "route": cfg.route, "layerwise": cfg.layerwise, "resident_receiver": bool(cfg.queue), "arrival_driven": cfg.ready_ms is not None,
         "gpus_visible": n_devices, "ranks": world, "oversubscribed": world > n_devices,
         "requests": len(reqs), "bytes_transferred": total, "wall_seconds": wall,
         "aggregate_throughput_GBps": total / wall / 1e9,

@@ -2,7 +2,8 @@
  * kvx_c_client.c — a host program in plain C (gcc, no CUDA headers, no Python, no torch) that drives
  * libkvx.so through include/kvx.h only, the way a non-Python serving engine would bind it: register
  * two KV pools, hand a request over with host block-id lists (kvx_handoff_host), repeat it through
- * the allocation-free entry (kvx_handoff_static), and compare every byte of both destination pools
+ * the allocation-free entry (kvx_handoff_static) and, in three parts, through the resident receiver
+ * (kvx_queue_start / submit / wait / stop), and compare every byte of the three destination pools
  * with the oracle's C restatement.  TEST CODE: it links the oracle, the library does not.
  *
  *   gcc -I include kvx_c_client.c -L <dir of libkvx.so> -lkvx -ldl
@@ -78,23 +79,32 @@ int main(int argc, char** argv) {
   for (uint64_t i = 0; i < pool_bytes; i += 8) { uint64_t v = rng(); memcpy(h_src + i, &v, 8); }
   for (uint64_t i = 0; i < pool_bytes; i += 2) { h_want[i] = 0xDE; h_want[i + 1] = 0xC0; }  /* canary 0xC0DE */
 
-  void *d_src = NULL, *d_dst = NULL, *d_dst2 = NULL;
-  if (kvx_mem_alloc(ctx, pool_bytes, &d_src) || kvx_mem_alloc(ctx, pool_bytes, &d_dst) || kvx_mem_alloc(ctx, pool_bytes, &d_dst2)) return 2;
-  if (cudaMemcpy(d_src, h_src, pool_bytes, 1) || cudaMemcpy(d_dst, h_want, pool_bytes, 1) || cudaMemcpy(d_dst2, h_want, pool_bytes, 1)) return 2;
+  void *d_src = NULL, *d_dst = NULL, *d_dst2 = NULL, *d_dst3 = NULL;
+  if (kvx_mem_alloc(ctx, pool_bytes, &d_src) || kvx_mem_alloc(ctx, pool_bytes, &d_dst) || kvx_mem_alloc(ctx, pool_bytes, &d_dst2) ||
+      kvx_mem_alloc(ctx, pool_bytes, &d_dst3))
+    return 2;
+  if (cudaMemcpy(d_src, h_src, pool_bytes, 1) || cudaMemcpy(d_dst, h_want, pool_bytes, 1) || cudaMemcpy(d_dst2, h_want, pool_bytes, 1) ||
+      cudaMemcpy(d_dst3, h_want, pool_bytes, 1))
+    return 2;
 
-  void *sb[REG], *db[REG], *db2[REG];
+  void *sb[REG], *db[REG], *db2[REG], *db3[REG];
   uint8_t *hsb[REG], *hdb[REG];
   for (int r = 0; r < REG; ++r) {
     sb[r] = (uint8_t*)d_src + (uint64_t)r * NB * chunk;  db[r] = (uint8_t*)d_dst + (uint64_t)r * NB * chunk;
     db2[r] = (uint8_t*)d_dst2 + (uint64_t)r * NB * chunk;
+    db3[r] = (uint8_t*)d_dst3 + (uint64_t)r * NB * chunk;
     hsb[r] = h_src + (uint64_t)r * NB * chunk;            hdb[r] = h_want + (uint64_t)r * NB * chunk;
   }
   kvx_pool_desc sd = {sizeof(kvx_pool_desc), REG, N, H, D, E, KVX_LAYOUT_HND, 0, 1, 0, NB, 0, sb};
   kvx_pool_desc dd = {sizeof(kvx_pool_desc), REG, N, H, D, E, KVX_LAYOUT_NHD, 0, 1, 0, NB, 0, db};
-  kvx_pool_desc dd2 = dd;
+  kvx_pool_desc dd2 = dd, dd3 = dd;
   dd2.base = db2;
-  kvx_pool *sp = NULL, *dp = NULL;
-  if ((rc = kvx_pool_register(ctx, &sd, &sp)) || (rc = kvx_pool_register(ctx, &dd, &dp))) { fprintf(stderr, "register: %s\n", kvx_strerror(rc)); return 2; }
+  dd3.base = db3;
+  kvx_pool *sp = NULL, *dp = NULL, *dp3 = NULL;
+  if ((rc = kvx_pool_register(ctx, &sd, &sp)) || (rc = kvx_pool_register(ctx, &dd, &dp)) || (rc = kvx_pool_register(ctx, &dd3, &dp3))) {
+    fprintf(stderr, "register: %s\n", kvx_strerror(rc));
+    return 2;
+  }
 
   int32_t ts[NREQ], td[NREQ];
   shuffled_ids(ts, NREQ, NB);
@@ -104,6 +114,16 @@ int main(int argc, char** argv) {
   if (rc) { fprintf(stderr, "kvx_handoff_host: %s\n", kvx_strerror(rc)); return 2; }
   rc = kvx_handoff_static(0, &sd, ts, &dd2, td, NREQ, NULL, NULL, 0, NULL);
   if (rc) { fprintf(stderr, "kvx_handoff_static: %s\n", kvx_strerror(rc)); return 2; }
+  /* the same request in three parts through the resident receiver: no launch per part, tickets instead of streams */
+  kvx_queue* q = NULL;
+  if ((rc = kvx_queue_start(ctx, sp, dp3, NULL, 0, 0, &q))) { fprintf(stderr, "kvx_queue_start: %s\n", kvx_strerror(rc)); return 2; }
+  uint64_t ticket = 0;
+  const uint32_t parts[3] = {20, 20, NREQ - 40};
+  for (uint32_t k = 0, at = 0; k < 3; at += parts[k], ++k)
+    if ((rc = kvx_queue_submit(q, ts + at, td + at, parts[k], NULL, 0, NULL, &ticket))) { fprintf(stderr, "kvx_queue_submit: %s\n", kvx_strerror(rc)); return 2; }
+  for (uint64_t t = ticket - 2; t <= ticket; ++t)
+    if ((rc = kvx_queue_wait(q, t, 5000))) { fprintf(stderr, "kvx_queue_wait: %s\n", kvx_strerror(rc)); return 2; }
+  if ((rc = kvx_queue_stop(q))) { fprintf(stderr, "kvx_queue_stop: %s\n", kvx_strerror(rc)); return 2; }
   if (cudaDeviceSynchronize() || kvx_ctx_check(ctx)) return 2;
   if (done != 7) { fprintf(stderr, "completion word %llu != 7\n", (unsigned long long)done); return 1; }
 
@@ -116,15 +136,17 @@ int main(int argc, char** argv) {
   if (memcmp(h_got, h_want, pool_bytes)) { fprintf(stderr, "kvx_handoff_host: destination pool differs from the oracle\n"); bad = 1; }
   if (cudaMemcpy(h_got, d_dst2, pool_bytes, 2)) return 2;
   if (memcmp(h_got, h_want, pool_bytes)) { fprintf(stderr, "kvx_handoff_static: destination pool differs from the oracle\n"); bad = 1; }
+  if (cudaMemcpy(h_got, d_dst3, pool_bytes, 2)) return 2;
+  if (memcmp(h_got, h_want, pool_bytes)) { fprintf(stderr, "kvx_queue_*: destination pool differs from the oracle\n"); bad = 1; }
   if (cudaMemcpy(h_got, d_src, pool_bytes, 2)) return 2;
   if (memcmp(h_got, h_src, pool_bytes)) { fprintf(stderr, "source pool was modified\n"); bad = 1; }
 
-  kvx_pool_release(sp); kvx_pool_release(dp);
-  kvx_mem_free(ctx, d_src); kvx_mem_free(ctx, d_dst); kvx_mem_free(ctx, d_dst2);
+  kvx_pool_release(sp); kvx_pool_release(dp); kvx_pool_release(dp3);
+  kvx_mem_free(ctx, d_src); kvx_mem_free(ctx, d_dst); kvx_mem_free(ctx, d_dst2); kvx_mem_free(ctx, d_dst3);
   kvx_ctx_destroy(ctx);
   free(h_src); free(h_want); free(h_got);
   if (bad) return 1;
-  printf("C client OK: %d blocks x %d regions x %llu B bit-exact through kvx_handoff_host and kvx_handoff_static\n", NREQ, REG,
+  printf("C client OK: %d blocks x %d regions x %llu B bit-exact through kvx_handoff_host, kvx_handoff_static and kvx_queue_*\n", NREQ, REG,
          (unsigned long long)chunk);
   return 0;
 }

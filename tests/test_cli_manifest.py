@@ -249,3 +249,18 @@ def test_runner_layerwise_handoff(tmp_path):
         res = json.load(open(out / name / "results.json"))
         assert res["summary"]["verified_bit_exact"] is True and res["summary"]["layerwise"] == 4
         assert all(q["added_after_prefill_ms"] is not None and q["added_after_prefill_ms"] >= 0 for q in res["decode_ranks"][0]["requests"])
+
+
+@pytest.mark.gpu
+def test_runner_through_the_resident_receiver(tmp_path):
+    """queue=1: the decode worker pulls every request through kvx_queue_* (no launch per request); every request and the
+    whole pool are verified as in every other run, and one flipped byte still fails the run."""
+    out = tmp_path / "r"
+    url = "kvx://local?prefill=1&decode=1&isl=128,512,2048&requests=14&concurrency=2&queue=1"
+    r = _run("-u", url, "-m", M1B, "-o", str(out), "-b", "q")
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    s = json.load(open(out / "q" / "results.json"))["summary"]
+    assert s["resident_receiver"] is True and s["verified_bit_exact"] is True and s["requests_verified"] == s["requests"] == 14
+    assert s["releases_observed"] == s["releases_expected"] == 14
+    r = _run("-u", url + "&corrupt=0,9", "-m", M1B, "-o", str(out), "-b", "qbad")
+    assert r.returncode == 1
