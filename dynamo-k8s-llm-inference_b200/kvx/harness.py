@@ -414,6 +414,9 @@ def run_rank(rank: int, plans: List[RankPlan], cfg: StreamConfig, group=None, wo
 
             use_queue = cfg.queue and cfg.batch <= 1 and len(srcs) == 1 and p_tp == d_tp and not gated
             tickets: Dict[int, int] = {}
+            if use_queue:   # the receivers exist before the clock starts (their set-up allocates and is not part of a request)
+                for pr in p_reps:
+                    w.pull_queue(pr * 1000 + srcs[0].p_rank)
 
             def issue(i: int, lane) -> None:
                 """Queue request i on a lane: one pull per source edge (fan-in when p_tp > d_tp), joined on lane[0]."""
