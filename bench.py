@@ -467,6 +467,10 @@ def run_single(args):
             rec["launch_stream_hbm_frac_measured"] = round(2 * b / (rec["launch_stream_us"] * 1e-6) / 1e9 / hbm_peak, 4)
             queue[str(s_isl)] = rec
         queue["ctas"], queue["kernel_launches_for_all_of_the_above"] = q.ctas, q.launches
+        for k_isl, rec_ in queue.items():   # next to the launched path in the ISL sweep: the same request through the receiver
+            if isinstance(rec_, dict) and k_isl in sweep:
+                sweep[k_isl]["through_resident_receiver"] = {"us_per_request_in_a_stream": rec_["queue_stream_us"],
+                                                             "hbm_frac_measured": rec_["queue_stream_hbm_frac_measured"]}
         q.park()
     torch.cuda.synchronize()
 

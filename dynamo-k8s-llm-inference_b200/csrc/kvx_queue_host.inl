@@ -271,7 +271,9 @@ int32_t kvx_queue_submit(kvx_queue* q, const int32_t* h_src_table, const int32_t
   if (*q->parked != 0) {
     *q->parked = 0;
     std::atomic_thread_fence(std::memory_order_seq_cst);
-    return queue_launch(q);
+    const int32_t rc = queue_launch(q);
+    if (rc) *q->parked = 1;  // nothing is resident: the next submit must try again (this request stays queued)
+    return rc;
   }
   return KVX_OK;
 } KVX_CATCH_ALL
