@@ -70,6 +70,8 @@ def test_two_process_handoff_over_ipc():
     r = _torchrun([], 29612)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "pull ok" in r.stdout and "pair ok" in r.stdout and "batch ok" in r.stdout
+    if torch.cuda.device_count() >= 2:   # with two devices every byte crossed NVLink: the ranks say which GPU they used
+        assert "rank 0 uses cuda:0" in r.stdout and "rank 1 uses cuda:1" in r.stdout, r.stdout[-2000:]
 
 
 @pytest.mark.gpu
