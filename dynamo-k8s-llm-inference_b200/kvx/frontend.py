@@ -46,7 +46,7 @@ class InProcessHandoff:
     the same device).  `handoff(isl)` moves one prompt's KV and returns (seconds, bytes, descriptors)."""
 
     def __init__(self, shape: KVShape, *, p_device: int = 0, d_device: Optional[int] = None, p_layout: int = 1,
-                 d_layout: int = 0, max_isl: int = 32768):
+                 d_layout: int = 0, max_isl: int = 32768, resident_receiver: bool = False):
         import torch
 
         from . import synth
@@ -66,6 +66,9 @@ class InProcessHandoff:
         self.lock = threading.Lock()
         self.seq = 0
         self.d_device = d_device
+        # chat-sized prompts are a few blocks: the decode worker then receives through its resident receiver
+        # (kvx_queue_*: no kernel launch per request) instead of one launch per request
+        self.resident_receiver = resident_receiver
 
     def handoff(self, isl: int) -> Tuple[float, int, int]:
         torch = self.torch
@@ -77,16 +80,22 @@ class InProcessHandoff:
             dst = self.d.blocks.allocate(rid, n)  # fresh decode slots
             try:
                 torch.cuda.set_device(self.d_device)
-                stream = torch.cuda.current_stream(self.d_device)
-                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                a.record(stream)
-                self.d.pull(0, src, dst, notify_slot=self.seq, value=self.seq, stream=stream)
-                b.record(stream)
-                b.synchronize()
+                if self.resident_receiver:
+                    t0 = time.perf_counter()
+                    ticket = self.d.pull_queued(0, src, dst, notify_slot=self.seq, value=self.seq)
+                    self.d.pull_queue(0).wait(ticket, 10000)
+                    secs = time.perf_counter() - t0   # submit -> completion word seen (there is no launch to bracket)
+                else:
+                    stream = torch.cuda.current_stream(self.d_device)
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record(stream)
+                    self.d.pull(0, src, dst, notify_slot=self.seq, value=self.seq, stream=stream)
+                    b.record(stream)
+                    b.synchronize()
+                    secs = a.elapsed_time(b) / 1e3
                 self.d.ctx.check()
                 if not self.p.poll(self.seq, self.seq):  # release written by the kernel's last CTA
                     raise RuntimeError("prefill blocks were not released")
-                secs = a.elapsed_time(b) / 1e3
             finally:
                 self.p.blocks.free(rid)
                 self.d.blocks.free(rid)
@@ -230,6 +239,8 @@ def main(argv=None) -> int:
     ap.add_argument("--manifest", help="DynamoGraphDeployment yaml: worker layouts come from its backend")
     ap.add_argument("--prefill-ms-per-ktoken", type=float, default=0.0)
     ap.add_argument("--itl-ms", type=float, default=0.0)
+    ap.add_argument("--resident-receiver", action="store_true",
+                    help="the decode worker receives through kvx_queue_* (a resident kernel) instead of one launch per request")
     args = ap.parse_args(argv)
     p_layout, d_layout = 1, 0
     if args.manifest:
@@ -239,7 +250,7 @@ def main(argv=None) -> int:
         if not topo.disaggregated:
             raise SystemExit("the manifest has no prefill/decode split")
         p_layout, d_layout = topo.role("prefill")[0].layout, topo.role("decode")[0].layout
-    backend = InProcessHandoff(KV_SHAPES[args.model], p_layout=p_layout, d_layout=d_layout)
+    backend = InProcessHandoff(KV_SHAPES[args.model], p_layout=p_layout, d_layout=d_layout, resident_receiver=args.resident_receiver)
     fe = Frontend(args.model, backend, prefill_ms_per_ktoken=args.prefill_ms_per_ktoken, itl_ms=args.itl_ms)
     srv = fe.serve(args.host, args.port)
     print(f"kvx frontend on http://{args.host}:{srv.server_address[1]}/v1/chat/completions (model {args.model})", flush=True)

@@ -89,12 +89,14 @@ def test_streaming_is_sse(server):
 
 
 @pytest.mark.gpu
-def test_frontend_runs_real_handoffs():
-    """Three conversations' worth of requests through the real prefill/decode workers."""
+@pytest.mark.parametrize("resident_receiver", [False, True], ids=["launch_per_request", "resident_receiver"])
+def test_frontend_runs_real_handoffs(resident_receiver):
+    """Three conversations' worth of requests through the real prefill/decode workers, with a launch per request and
+    through the decode worker's resident receiver."""
     import kvx
     from kvx.frontend import InProcessHandoff
 
-    be = InProcessHandoff(kvx.KV_SHAPES["meta-llama/Llama-3.2-1B-Instruct"], max_isl=4096)
+    be = InProcessHandoff(kvx.KV_SHAPES["meta-llama/Llama-3.2-1B-Instruct"], max_isl=4096, resident_receiver=resident_receiver)
     fe = Frontend("meta-llama/Llama-3.2-1B-Instruct", be)
     srv = fe.serve("127.0.0.1", 0)
     base = f"http://127.0.0.1:{srv.server_address[1]}"
